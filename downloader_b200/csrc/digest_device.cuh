@@ -1,0 +1,326 @@
+// digest_device.cuh — sm_100a device code for the byte-integrity kernels.
+//
+// One thread = one message (Merkle–Damgård chains are sequential), one warp = 32 messages.
+// Each lane's message is staged HBM -> shared memory with 1-D bulk async copies
+// (cp.async.bulk, SASS UBLKCP) that complete on a per-warp mbarrier, double/triple buffered, and
+// read back as LDS.128.  The compression functions are written so ptxas emits LOP3 for every
+// 3-input boolean and SHF for every rotate.
+//
+// What it replaces (there is no reference source for the arithmetic — it is OpenSSL behind Node
+// crypto): sha1 per piece ([dep] simple-sha1@2.1.2 via webtorrent, call site lib/download.js:64-66),
+// md5 / sha256 per part ([dep] minio@7.0.12 getHashSummer, call site lib/upload.js:45,55).
+// Algorithms: FIPS 180-4 §6.1 (SHA-1), §6.2 (SHA-256), RFC 1321 (MD5).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace th {
+
+// ------------------------------------------------------------------------------------ primitives
+template <int LUT>
+__device__ __forceinline__ uint32_t lop3(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;
+  asm("lop3.b32 %0, %1, %2, %3, %4;" : "=r"(r) : "r"(a), "r"(b), "r"(c), "n"(LUT));
+  return r;
+}
+__device__ __forceinline__ uint32_t rotl(uint32_t x, int n) { return __funnelshift_l(x, x, n); }
+__device__ __forceinline__ uint32_t rotr(uint32_t x, int n) { return __funnelshift_r(x, x, n); }
+__device__ __forceinline__ uint32_t bswap(uint32_t x) { return __byte_perm(x, 0, 0x0123); }
+
+constexpr int LUT_CH = 0xCA;   // (a & b) | (~a & c)
+constexpr int LUT_MAJ = 0xE8;  // majority
+constexpr int LUT_XOR3 = 0x96; // a ^ b ^ c
+constexpr int LUT_MD5I = 0x39; // b ^ (a | ~c)   with (a,b,c) = (b,c,d) of RFC 1321's I(b,c,d) = c ^ (b | ~d)
+
+// ---------------------------------------------------------------------------------------- SHA-1
+struct Sha1 {
+  static constexpr int NS = 5, DLEN = 20;
+  static constexpr bool BE = true;
+  __device__ static __forceinline__ void init(uint32_t* h) {
+    h[0] = 0x67452301u; h[1] = 0xefcdab89u; h[2] = 0x98badcfeu; h[3] = 0x10325476u; h[4] = 0xc3d2e1f0u;
+  }
+  // w: 16 big-endian-decoded words; used as the rolling schedule window (destroyed).
+  __device__ static __forceinline__ void compress(uint32_t* h, uint32_t* w) {
+    uint32_t a = h[0], b = h[1], c = h[2], d = h[3], e = h[4];
+#pragma unroll
+    for (int t = 0; t < 80; t++) {
+      if (t >= 16)
+        w[t & 15] = rotl(lop3<LUT_XOR3>(w[(t - 3) & 15], w[(t - 8) & 15], w[(t - 14) & 15]) ^ w[t & 15], 1);
+      uint32_t f, k;
+      if (t < 20)      { f = lop3<LUT_CH>(b, c, d);   k = 0x5a827999u; }
+      else if (t < 40) { f = lop3<LUT_XOR3>(b, c, d); k = 0x6ed9eba1u; }
+      else if (t < 60) { f = lop3<LUT_MAJ>(b, c, d);  k = 0x8f1bbcdcu; }
+      else             { f = lop3<LUT_XOR3>(b, c, d); k = 0xca62c1d6u; }
+      uint32_t ekw = e + k + w[t & 15];       // off the critical path
+      uint32_t tmp = rotl(a, 5) + f + ekw;
+      e = d; d = c; c = rotl(b, 30); b = a; a = tmp;
+    }
+    h[0] += a; h[1] += b; h[2] += c; h[3] += d; h[4] += e;
+  }
+};
+
+// ------------------------------------------------------------------------------------------ MD5
+struct Md5 {
+  static constexpr int NS = 4, DLEN = 16;
+  static constexpr bool BE = false;
+  __device__ static __forceinline__ void init(uint32_t* h) {
+    h[0] = 0x67452301u; h[1] = 0xefcdab89u; h[2] = 0x98badcfeu; h[3] = 0x10325476u;
+  }
+  template <int I>
+  __device__ static __forceinline__ void step(uint32_t& a, uint32_t b, uint32_t c, uint32_t d,
+                                              const uint32_t* m) {
+    constexpr uint32_t T[64] = {
+        0xd76aa478, 0xe8c7b756, 0x242070db, 0xc1bdceee, 0xf57c0faf, 0x4787c62a, 0xa8304613, 0xfd469501,
+        0x698098d8, 0x8b44f7af, 0xffff5bb1, 0x895cd7be, 0x6b901122, 0xfd987193, 0xa679438e, 0x49b40821,
+        0xf61e2562, 0xc040b340, 0x265e5a51, 0xe9b6c7aa, 0xd62f105d, 0x02441453, 0xd8a1e681, 0xe7d3fbc8,
+        0x21e1cde6, 0xc33707d6, 0xf4d50d87, 0x455a14ed, 0xa9e3e905, 0xfcefa3f8, 0x676f02d9, 0x8d2a4c8a,
+        0xfffa3942, 0x8771f681, 0x6d9d6122, 0xfde5380c, 0xa4beea44, 0x4bdecfa9, 0xf6bb4b60, 0xbebfbc70,
+        0x289b7ec6, 0xeaa127fa, 0xd4ef3085, 0x04881d05, 0xd9d4d039, 0xe6db99e5, 0x1fa27cf8, 0xc4ac5665,
+        0xf4292244, 0x432aff97, 0xab9423a7, 0xfc93a039, 0x655b59c3, 0x8f0ccc92, 0xffeff47d, 0x85845dd1,
+        0x6fa87e4f, 0xfe2ce6e0, 0xa3014314, 0x4e0811a1, 0xf7537e82, 0xbd3af235, 0x2ad7d2bb, 0xeb86d391};
+    constexpr int S[16] = {7, 12, 17, 22, 5, 9, 14, 20, 4, 11, 16, 23, 6, 10, 15, 21};
+    constexpr int R = I >> 4;
+    constexpr int G = R == 0 ? I : R == 1 ? (5 * I + 1) & 15 : R == 2 ? (3 * I + 5) & 15 : (7 * I) & 15;
+    uint32_t f = R == 0   ? lop3<LUT_CH>(b, c, d)
+                 : R == 1 ? lop3<LUT_CH>(d, b, c)
+                 : R == 2 ? lop3<LUT_XOR3>(b, c, d)
+                          : lop3<LUT_MD5I>(b, c, d);
+    uint32_t akm = a + T[I] + m[G];  // off the critical path
+    a = b + rotl(akm + f, S[(R << 2) | (I & 3)]);
+  }
+  template <int I>
+  __device__ static __forceinline__ void four(uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d,
+                                              const uint32_t* m) {
+    step<I>(a, b, c, d, m);
+    step<I + 1>(d, a, b, c, m);
+    step<I + 2>(c, d, a, b, m);
+    step<I + 3>(b, c, d, a, m);
+  }
+  // w: 16 little-endian words (not modified).
+  __device__ static __forceinline__ void compress(uint32_t* h, const uint32_t* m) {
+    uint32_t a = h[0], b = h[1], c = h[2], d = h[3];
+    four<0>(a, b, c, d, m);  four<4>(a, b, c, d, m);  four<8>(a, b, c, d, m);  four<12>(a, b, c, d, m);
+    four<16>(a, b, c, d, m); four<20>(a, b, c, d, m); four<24>(a, b, c, d, m); four<28>(a, b, c, d, m);
+    four<32>(a, b, c, d, m); four<36>(a, b, c, d, m); four<40>(a, b, c, d, m); four<44>(a, b, c, d, m);
+    four<48>(a, b, c, d, m); four<52>(a, b, c, d, m); four<56>(a, b, c, d, m); four<60>(a, b, c, d, m);
+    h[0] += a; h[1] += b; h[2] += c; h[3] += d;
+  }
+};
+
+// -------------------------------------------------------------------------------------- SHA-256
+struct Sha256 {
+  static constexpr int NS = 8, DLEN = 32;
+  static constexpr bool BE = true;
+  __device__ static __forceinline__ void init(uint32_t* h) {
+    h[0] = 0x6a09e667u; h[1] = 0xbb67ae85u; h[2] = 0x3c6ef372u; h[3] = 0xa54ff53au;
+    h[4] = 0x510e527fu; h[5] = 0x9b05688cu; h[6] = 0x1f83d9abu; h[7] = 0x5be0cd19u;
+  }
+  __device__ static __forceinline__ void compress(uint32_t* h, uint32_t* w) {
+    constexpr uint32_t K[64] = {
+        0x428a2f98, 0x71374491, 0xb5c0fbcf, 0xe9b5dba5, 0x3956c25b, 0x59f111f1, 0x923f82a4, 0xab1c5ed5,
+        0xd807aa98, 0x12835b01, 0x243185be, 0x550c7dc3, 0x72be5d74, 0x80deb1fe, 0x9bdc06a7, 0xc19bf174,
+        0xe49b69c1, 0xefbe4786, 0x0fc19dc6, 0x240ca1cc, 0x2de92c6f, 0x4a7484aa, 0x5cb0a9dc, 0x76f988da,
+        0x983e5152, 0xa831c66d, 0xb00327c8, 0xbf597fc7, 0xc6e00bf3, 0xd5a79147, 0x06ca6351, 0x14292967,
+        0x27b70a85, 0x2e1b2138, 0x4d2c6dfc, 0x53380d13, 0x650a7354, 0x766a0abb, 0x81c2c92e, 0x92722c85,
+        0xa2bfe8a1, 0xa81a664b, 0xc24b8b70, 0xc76c51a3, 0xd192e819, 0xd6990624, 0xf40e3585, 0x106aa070,
+        0x19a4c116, 0x1e376c08, 0x2748774c, 0x34b0bcb5, 0x391c0cb3, 0x4ed8aa4a, 0x5b9cca4f, 0x682e6ff3,
+        0x748f82ee, 0x78a5636f, 0x84c87814, 0x8cc70208, 0x90befffa, 0xa4506ceb, 0xbef9a3f7, 0xc67178f2};
+    uint32_t a = h[0], b = h[1], c = h[2], d = h[3], e = h[4], f = h[5], g = h[6], hh = h[7];
+#pragma unroll
+    for (int t = 0; t < 64; t++) {
+      if (t >= 16) {
+        uint32_t x = w[(t - 15) & 15], y = w[(t - 2) & 15];
+        uint32_t s0 = lop3<LUT_XOR3>(rotr(x, 7), rotr(x, 18), x >> 3);
+        uint32_t s1 = lop3<LUT_XOR3>(rotr(y, 17), rotr(y, 19), y >> 10);
+        w[t & 15] = w[t & 15] + s0 + w[(t - 7) & 15] + s1;
+      }
+      uint32_t S1 = lop3<LUT_XOR3>(rotr(e, 6), rotr(e, 11), rotr(e, 25));
+      uint32_t t1 = hh + K[t] + w[t & 15];  // off the critical path
+      t1 = t1 + S1 + lop3<LUT_CH>(e, f, g);
+      uint32_t S0 = lop3<LUT_XOR3>(rotr(a, 2), rotr(a, 13), rotr(a, 22));
+      uint32_t t2 = S0 + lop3<LUT_MAJ>(a, b, c);
+      hh = g; g = f; f = e; e = d + t1; d = c; c = b; b = a; a = t1 + t2;
+    }
+    h[0] += a; h[1] += b; h[2] += c; h[3] += d; h[4] += e; h[5] += f; h[6] += g; h[7] += hh;
+  }
+};
+
+// ------------------------------------------------------------------- shared memory / TMA helpers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_init_fence() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "TH_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra TH_DONE;\n"
+      "bra TH_WAIT;\n"
+      "TH_DONE:\n"
+      "}\n" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+// 1-D bulk async copy global -> this CTA's shared memory, completing `bytes` on the mbarrier.
+// dst, src 16-byte aligned; bytes a non-zero multiple of 16.
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_smem() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts8(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
+// ------------------------------------------------------------------------------- padding blocks
+// Turns the 16 little-endian-loaded words of the block that holds the message tail (r = len % 64
+// valid bytes, anything after them garbage) into padding block `k` (0 or 1) of the message:
+// 0x80, zeros, 64-bit bit length — little-endian for MD5, big-endian for SHA-1/SHA-256
+// (RFC 1321 §3.1-3.2, FIPS 180-4 §5.1.1).  For BE digests the length words are pre-swapped because
+// the caller byte-swaps all 16 words afterwards.
+template <class A>
+__device__ __forceinline__ void pad_block(uint32_t* w, uint32_t k, uint32_t r, uint64_t len) {
+  const bool one_block = r < 56;
+  if (k == 0) {
+    const uint32_t wi = r >> 2, sh = (r & 3) * 8;
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+      uint32_t keep = (uint32_t)i < wi ? w[i] : 0u;
+      uint32_t edge = (w[i] & ((1u << sh) - 1u)) | (0x80u << sh);
+      w[i] = (uint32_t)i == wi ? edge : keep;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 16; i++) w[i] = 0u;
+  }
+  if (k == 1 || one_block) {
+    const uint64_t bits = len << 3;
+    const uint32_t lo = (uint32_t)bits, hi = (uint32_t)(bits >> 32);
+    if (A::BE) { w[14] = bswap(hi); w[15] = bswap(lo); }
+    else       { w[14] = lo;        w[15] = hi; }
+  }
+}
+
+// ------------------------------------------------------------------------------ the stream engine
+// Per-warp staging geometry.  CH = bytes staged per lane per stage (multiple of 64), NST = stages.
+// Lane slots are CH+16 bytes apart so that the eight 16-byte reads of each LDS.128 quarter-warp
+// phase fall in eight different 16-byte bank groups (stride = 16 mod 128 when CH % 128 == 0, an odd
+// multiple of 16 otherwise is also conflict-free).
+template <int CH, int NST>
+struct Staging {
+  static_assert(CH % 64 == 0 && CH >= 64 && CH <= 1024, "chunk must be a multiple of 64");
+  static_assert(((CH + 16) / 16) % 2 == 1, "lane stride must be an odd multiple of 16 bytes");
+  static constexpr int STRIDE = CH + 16;
+  static constexpr int STAGE_BYTES = 32 * STRIDE;
+  static constexpr int WARP_BYTES = NST * STAGE_BYTES + 8 * NST;  // + mbarriers
+};
+
+// Hashes one message per lane.  msg is 16-byte aligned (or anything if len == 0).
+// smem: this warp's Staging<CH,NST>::WARP_BYTES region (16-byte aligned).
+template <class A, int CH, int NST>
+__device__ __forceinline__ void digest_stream(const uint8_t* __restrict__ msg, uint64_t len, uint32_t* h,
+                                              unsigned char* smem, int lane) {
+  using G = Staging<CH, NST>;
+  constexpr unsigned FULL = 0xffffffffu;
+  const uint32_t s_base = smem_u32(smem);
+  const uint32_t s_bar = s_base + NST * G::STAGE_BYTES;
+  const uint32_t s_lane = s_base + lane * G::STRIDE;
+
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < NST; s++) mbar_init(s_bar + 8 * s, 1);
+    mbar_init_fence();
+  }
+  __syncwarp();
+
+  // chunk c covers message bytes [c*CH, min((c+1)*CH, len)); every lane has nch >= 1 chunks and its
+  // last chunk is partial (possibly empty) and is followed by the padding block(s).
+  const uint32_t nch = (uint32_t)(len / CH) + 1u;
+  const uint32_t last_bytes = (uint32_t)(len - (uint64_t)(nch - 1u) * CH);
+  const uint32_t max_nch = __reduce_max_sync(FULL, nch);
+
+  auto issue = [&](uint32_t c, int s) {
+    uint32_t bytes = c < nch ? (c == nch - 1u ? last_bytes : (uint32_t)CH) : 0u;
+    const uint32_t tb = bytes & ~15u;
+    const uint32_t total = __reduce_add_sync(FULL, tb);
+    if (c < max_nch) {  // warp-uniform
+      const uint32_t bar = s_bar + 8 * s;
+      const uint32_t dst = s_lane + s * G::STAGE_BYTES;
+      const uint8_t* src = msg + (uint64_t)c * CH;
+      if (lane == 0) mbar_arrive_expect_tx(bar, total);
+      __syncwarp();
+      if (tb) bulk_g2s(dst, src, tb, bar);
+      // a tail shorter than 16 bytes cannot be bulk-copied: move it by hand (last chunk only)
+      for (uint32_t j = tb; j < bytes; j++) sts8(dst + j, __ldg(src + j));
+    }
+  };
+
+#pragma unroll
+  for (int s = 0; s < NST; s++) issue((uint32_t)s, s);
+
+  A::init(h);
+  int s = 0;
+  uint32_t parity = 0;
+  for (uint32_t c = 0; c < max_nch; c++) {
+    mbar_wait(s_bar + 8 * s, parity);
+    if (c < nch) {
+      const bool last = c == nch - 1u;
+      const uint32_t bytes = last ? last_bytes : (uint32_t)CH;
+      const uint32_t nb = bytes >> 6;                      // whole data blocks in this chunk
+      const uint32_t r = bytes & 63u;                      // tail bytes (last chunk only)
+      const uint32_t nblk = nb + (last ? (r < 56 ? 1u : 2u) : 0u);
+      const uint32_t src = s_lane + s * G::STAGE_BYTES;
+      for (uint32_t b = 0; b < nblk; b++) {
+        uint32_t w[16];
+        // padding block 1 may lie one block past the slot when the tail sits in the slot's last
+        // block; it is all zeros + length, so nothing needs to be read for it
+        const uint32_t a = src + (b < (uint32_t)(CH / 64) ? b : 0u) * 64u;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+          uint4 v = lds128(a + 16 * q);
+          w[4 * q] = v.x; w[4 * q + 1] = v.y; w[4 * q + 2] = v.z; w[4 * q + 3] = v.w;
+        }
+        if (b >= nb) pad_block<A>(w, b - nb, r, len);
+        if (A::BE) {
+#pragma unroll
+          for (int i = 0; i < 16; i++) w[i] = bswap(w[i]);
+        }
+        A::compress(h, w);
+      }
+    }
+    __syncwarp();
+    // every value read from this stage has been consumed by compress(); order those generic-proxy
+    // reads before the async-proxy refill of the same bytes
+    fence_proxy_async_smem();
+    issue(c + NST, s);
+    if (++s == NST) { s = 0; parity ^= 1u; }
+  }
+}
+
+// Writes the digest in its standard byte order (SHA: big-endian words; MD5: little-endian words).
+template <class A>
+__device__ __forceinline__ void store_digest(uint8_t* out, const uint32_t* h) {
+  uint32_t* o = reinterpret_cast<uint32_t*>(out);  // 4-byte aligned: out + i*{20,16,32}
+#pragma unroll
+  for (int i = 0; i < A::NS; i++) o[i] = A::BE ? bswap(h[i]) : h[i];
+}
+
+}  // namespace th

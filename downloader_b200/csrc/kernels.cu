@@ -1,0 +1,271 @@
+// kernels.cu — sm_100a kernels and the launch-level C ABI (include/tritonhash.h, last section).
+//
+//   digest_kernel<A,CH,NST>  one warp = one CTA = 32 messages; th::digest_stream does the work.
+//                            SHA-1 adds the fused compare -> verified bitfield ([dep] webtorrent
+//                            `hash === _hashes[index]` -> bitfield.set(index); lib/download.js:64-66).
+//   etag_kernel              one warp per multipart object, md5 over its part digests, message words
+//                            exchanged by warp shuffle (S3 ETag returned to [dep] minio
+//                            completeMultipartUpload; lib/upload.js:45).
+//   synth_kernel             SURVEY §8d counter-based generator (benchmarks / tests).
+#include <cstdint>
+#include <cstdio>
+#include <cuda_runtime.h>
+
+#include "../../include/tritonhash.h"
+#include "digest_device.cuh"
+
+namespace th {
+
+struct DigestArgs {
+  const uint8_t* base;
+  const uint64_t* offsets;  // nullable -> i * stride
+  const uint64_t* lengths;  // nullable -> len
+  const uint32_t* order;    // nullable -> identity
+  uint64_t stride, len;
+  uint32_t n;
+  uint8_t* out;
+  const uint8_t* expected;  // SHA-1 only, nullable
+  uint32_t* ok_bits;        // SHA-1 only, nullable
+};
+
+template <class A, int CH, int NST>
+__global__ void __launch_bounds__(32) digest_kernel(const DigestArgs p) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int lane = threadIdx.x;
+  const uint32_t slot = blockIdx.x * 32u + lane;
+  const bool valid = slot < p.n;
+  uint32_t idx = slot;
+  if (valid && p.order) idx = p.order[slot];
+  uint64_t off = 0, len = 0;
+  if (valid) {
+    off = p.offsets ? p.offsets[idx] : (uint64_t)idx * p.stride;
+    len = p.lengths ? p.lengths[idx] : p.len;
+  }
+  uint32_t h[A::NS];
+  digest_stream<A, CH, NST>(p.base + off, len, h, smem, lane);
+  if (valid) store_digest<A>(p.out + (size_t)idx * A::DLEN, h);
+
+  if (A::DLEN == 20 && p.expected && p.ok_bits) {  // fused piece verification
+    bool ok = false;
+    if (valid) {
+      const uint32_t* e = reinterpret_cast<const uint32_t*>(p.expected + (size_t)idx * 20);
+      ok = true;
+#pragma unroll
+      for (int i = 0; i < 5; i++) ok &= (__ldg(e + i) == bswap(h[i]));
+    }
+    if (p.order) {
+      if (ok) atomicOr(p.ok_bits + (idx >> 5), 1u << (idx & 31));
+    } else {
+      const uint32_t word = __ballot_sync(0xffffffffu, ok);
+      if (lane == 0) p.ok_bits[blockIdx.x] = word;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------ ETag combine
+// One warp per object.  The message is the object's part digests back to back (N*16 bytes, so the
+// tail is 0/16/32/48 bytes and there is always exactly one padding block).  Each iteration the warp
+// loads a 128-byte window (two MD5 blocks) with one coalesced 4-byte load per lane; every lane runs
+// the same chain and fetches message word g from lane g (block A) / 16+g (block B) by shuffle.
+struct Md5Shfl {
+  template <int I>
+  __device__ static __forceinline__ void step(uint32_t& a, uint32_t b, uint32_t c, uint32_t d, uint32_t mine,
+                                              int half) {
+    constexpr int R = I >> 4;
+    constexpr int G = R == 0 ? I : R == 1 ? (5 * I + 1) & 15 : R == 2 ? (3 * I + 5) & 15 : (7 * I) & 15;
+    uint32_t m[16];
+    m[G] = __shfl_sync(0xffffffffu, mine, half * 16 + G);
+    Md5::step<I>(a, b, c, d, m);
+  }
+  template <int I>
+  __device__ static __forceinline__ void four(uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d, uint32_t mine,
+                                              int half) {
+    step<I>(a, b, c, d, mine, half);
+    step<I + 1>(d, a, b, c, mine, half);
+    step<I + 2>(c, d, a, b, mine, half);
+    step<I + 3>(b, c, d, a, mine, half);
+  }
+  __device__ static __forceinline__ void block(uint32_t* h, uint32_t mine, int half) {
+    uint32_t a = h[0], b = h[1], c = h[2], d = h[3];
+    four<0>(a, b, c, d, mine, half);  four<4>(a, b, c, d, mine, half);  four<8>(a, b, c, d, mine, half);
+    four<12>(a, b, c, d, mine, half); four<16>(a, b, c, d, mine, half); four<20>(a, b, c, d, mine, half);
+    four<24>(a, b, c, d, mine, half); four<28>(a, b, c, d, mine, half); four<32>(a, b, c, d, mine, half);
+    four<36>(a, b, c, d, mine, half); four<40>(a, b, c, d, mine, half); four<44>(a, b, c, d, mine, half);
+    four<48>(a, b, c, d, mine, half); four<52>(a, b, c, d, mine, half); four<56>(a, b, c, d, mine, half);
+    four<60>(a, b, c, d, mine, half);
+    h[0] += a; h[1] += b; h[2] += c; h[3] += d;
+  }
+};
+
+__global__ void __launch_bounds__(128) etag_kernel(const uint8_t* __restrict__ md5s,
+                                                   const uint64_t* __restrict__ prefix, uint32_t n_objects,
+                                                   uint8_t* __restrict__ out) {
+  const uint32_t obj = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (obj >= n_objects) return;  // warp-uniform
+  const uint64_t first = prefix[obj], parts = prefix[obj + 1] - first;
+  const uint32_t* msg = reinterpret_cast<const uint32_t*>(md5s + first * 16);
+  const uint64_t nwords = parts * 4;        // message words
+  const uint64_t nblocks = parts / 4 + 1;   // data blocks + the one padding block
+  const uint64_t bits = parts * 128;
+  const uint64_t len_word = (nblocks - 1) * 16 + 14;
+  uint32_t h[4];
+  Md5::init(h);
+  for (uint64_t wb = 0; wb < nblocks; wb += 2) {
+    const uint64_t g = wb * 16 + lane;
+    uint32_t mine = 0;
+    if (g < nwords) mine = __ldg(msg + g);
+    else if (g == nwords) mine = 0x80u;
+    if (g == len_word) mine = (uint32_t)bits;
+    if (g == len_word + 1) mine = (uint32_t)(bits >> 32);
+    Md5Shfl::block(h, mine, 0);
+    if (wb + 1 < nblocks) Md5Shfl::block(h, mine, 1);
+  }
+  const uint32_t v = lane == 0 ? h[0] : lane == 1 ? h[1] : lane == 2 ? h[2] : h[3];
+  if (lane < 4) reinterpret_cast<uint32_t*>(out + (size_t)obj * 16)[lane] = v;
+}
+
+// ------------------------------------------------------------------------------------ synthetic data
+__device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
+  x += 0x9e3779b97f4a7c15ull;
+  x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ull;
+  x = (x ^ (x >> 27)) * 0x94d049bb133111ebull;
+  return x ^ (x >> 31);
+}
+
+__global__ void __launch_bounds__(256) synth_kernel(uint8_t* __restrict__ dst, uint64_t first_msg, uint64_t n,
+                                                    uint64_t len, uint64_t stride, uint64_t seed) {
+  const uint64_t words_per_msg = (len + 7) / 8;
+  const uint64_t total = n * words_per_msg;
+  for (uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t k = t / words_per_msg, j = t - k * words_per_msg;
+    const uint64_t w = splitmix64(seed + ((first_msg + k) << 40) + j);
+    uint8_t* p = dst + k * stride + j * 8;
+    const uint64_t left = len - j * 8;
+    if (left >= 8 && (reinterpret_cast<uintptr_t>(p) & 7) == 0) {
+      *reinterpret_cast<uint64_t*>(p) = w;
+    } else {
+      for (uint64_t b = 0; b < (left < 8 ? left : 8); b++) p[b] = (uint8_t)(w >> (8 * b));
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------ dispatch
+using launch_fn = cudaError_t (*)(const DigestArgs&, cudaStream_t);
+
+template <class A, int CH, int NST>
+cudaError_t launch_variant(const DigestArgs& a, cudaStream_t st) {
+  constexpr int smem = Staging<CH, NST>::WARP_BYTES;
+  static bool attr_set[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (smem > 48 * 1024 && dev < 64 && !attr_set[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(digest_kernel<A, CH, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    attr_set[dev] = true;
+  }
+  const uint32_t grid = (a.n + 31u) / 32u;
+  digest_kernel<A, CH, NST><<<grid, 32, smem, st>>>(a);
+  return cudaGetLastError();
+}
+
+struct Variant { int ch, nst; launch_fn fn[3]; };
+#define TH_VARIANT(CH, NST) \
+  { CH, NST, { launch_variant<Sha1, CH, NST>, launch_variant<Md5, CH, NST>, launch_variant<Sha256, CH, NST> } }
+static const Variant g_variants[] = {
+    TH_VARIANT(64, 4),  TH_VARIANT(128, 2), TH_VARIANT(128, 3), TH_VARIANT(128, 4),
+    TH_VARIANT(256, 2), TH_VARIANT(256, 3), TH_VARIANT(512, 2),
+};
+constexpr int kNumVariants = sizeof(g_variants) / sizeof(g_variants[0]);
+static int g_selected[3] = {2, 2, 2};  // index into g_variants per algorithm: sha1, md5, sha256
+
+static int alg_index(uint32_t alg) {
+  return alg == TH_ALG_SHA1 ? 0 : alg == TH_ALG_MD5 ? 1 : alg == TH_ALG_SHA256 ? 2 : -1;
+}
+
+static int launch_digest(uint32_t alg, const void* d_base, const uint64_t* d_offsets, const uint64_t* d_lengths,
+                         const uint32_t* d_order, uint64_t stride, uint64_t len, uint32_t n, uint8_t* d_out,
+                         const uint8_t* d_expected, uint32_t* d_ok_bits, void* stream) {
+  const int ai = alg_index(alg);
+  if (ai < 0 || !d_out) return TH_EINVAL;
+  if (n == 0) return TH_OK;
+  if (!d_base && !(d_lengths == nullptr && len == 0)) return TH_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(d_base) & 15) != 0) return TH_EALIGN;
+  if (!d_offsets && (stride & 15) != 0 && n > 1) return TH_EALIGN;
+  if (!d_lengths && len >= (1ull << 37)) return TH_ETOOBIG;
+  DigestArgs a{static_cast<const uint8_t*>(d_base), d_offsets, d_lengths, d_order, stride, len, n, d_out,
+               d_expected, d_ok_bits};
+  cudaError_t e = g_variants[g_selected[ai]].fn[ai](a, static_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? TH_OK : TH_ECUDA;
+}
+
+}  // namespace th
+
+// ----------------------------------------------------------------------------------------- C ABI
+extern "C" {
+
+int th_sha1_batch(const void* d_base, const uint64_t* d_offsets, const uint64_t* d_lengths,
+                  const uint32_t* d_order, uint64_t stride, uint64_t len, uint32_t n, uint8_t* d_out20,
+                  const uint8_t* d_expected20, uint32_t* d_ok_bits, void* stream) {
+  return th::launch_digest(TH_ALG_SHA1, d_base, d_offsets, d_lengths, d_order, stride, len, n, d_out20,
+                           d_expected20, d_ok_bits, stream);
+}
+
+int th_md5_batch(const void* d_base, const uint64_t* d_offsets, const uint64_t* d_lengths,
+                 const uint32_t* d_order, uint64_t stride, uint64_t len, uint32_t n, uint8_t* d_out16,
+                 void* stream) {
+  return th::launch_digest(TH_ALG_MD5, d_base, d_offsets, d_lengths, d_order, stride, len, n, d_out16, nullptr,
+                           nullptr, stream);
+}
+
+int th_sha256_batch(const void* d_base, const uint64_t* d_offsets, const uint64_t* d_lengths,
+                    const uint32_t* d_order, uint64_t stride, uint64_t len, uint32_t n, uint8_t* d_out32,
+                    void* stream) {
+  return th::launch_digest(TH_ALG_SHA256, d_base, d_offsets, d_lengths, d_order, stride, len, n, d_out32,
+                           nullptr, nullptr, stream);
+}
+
+int th_etag_combine_device(const uint8_t* d_md5s, const uint64_t* d_part_prefix, uint32_t n_objects,
+                           uint8_t* d_out16, void* stream) {
+  if (!d_part_prefix || !d_out16) return TH_EINVAL;
+  if (n_objects == 0) return TH_OK;
+  if ((reinterpret_cast<uintptr_t>(d_md5s) & 3) != 0) return TH_EALIGN;
+  const uint32_t warps = 4;
+  th::etag_kernel<<<(n_objects + warps - 1) / warps, warps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+      d_md5s, d_part_prefix, n_objects, d_out16);
+  return cudaGetLastError() == cudaSuccess ? TH_OK : TH_ECUDA;
+}
+
+int th_synth_fill(void* d_dst, uint64_t first_msg, uint64_t n, uint64_t len, uint64_t stride, uint64_t seed,
+                  void* stream) {
+  if (!d_dst) return TH_EINVAL;
+  if (n == 0 || len == 0) return TH_OK;
+  const uint64_t total = n * ((len + 7) / 8);
+  uint64_t blocks = (total + 255) / 256;
+  if (blocks > 148ull * 64) blocks = 148ull * 64;
+  th::synth_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<uint8_t*>(d_dst), first_msg, n, len, stride, seed);
+  return cudaGetLastError() == cudaSuccess ? TH_OK : TH_ECUDA;
+}
+
+int th_set_staging(uint32_t alg, int chunk_bytes, int stages) {
+  int rc = TH_EINVAL;
+  for (int v = 0; v < th::kNumVariants; v++) {
+    if (th::g_variants[v].ch == chunk_bytes && th::g_variants[v].nst == stages) {
+      for (int a = 0; a < 3; a++)
+        if (alg & (1u << a)) { th::g_selected[a] = v; rc = TH_OK; }
+    }
+  }
+  return rc;
+}
+
+int th_get_staging(uint32_t alg, int* chunk_bytes, int* stages) {
+  const int ai = th::alg_index(alg);
+  if (ai < 0) return TH_EINVAL;
+  if (chunk_bytes) *chunk_bytes = th::g_variants[th::g_selected[ai]].ch;
+  if (stages) *stages = th::g_variants[th::g_selected[ai]].nst;
+  return TH_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,600 @@
+// runtime.cu — host side of libtritonhash.so: contexts, pinned rings, streams, tickets.
+//
+// What it stands in for: nothing in tritonmedia/downloader allocates or schedules for hashing —
+// [dep] webtorrent hands a piece Buffer to sha1(buf, cb) and [dep] minio pipes a part range through
+// getHashSummer, both synchronously on Node's one event-loop thread.  Here a
+// batch of such buffers becomes: pinned ring slot -> one cudaMemcpyAsync H2D -> one digest kernel per
+// requested algorithm (each on its own stream, so MD5 and SHA-256 of the same parts overlap) ->
+// cudaMemcpyAsync D2H of the 16..32-byte digests.  Everything is enqueued by th_submit and never
+// blocks; rings are double-buffered simply by holding two or more slots in flight.
+//
+// There is no CPU fallback: every path ends in a kernel of kernels.cu or fails with an error code.
+#include <algorithm>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <deque>
+#include <mutex>
+#include <numeric>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "../../include/tritonhash.h"
+
+namespace {
+
+constexpr size_t kRingAlign = 256;
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// Per-submit staging: one pinned block + one device block, carved identically.
+//   [offsets n*8][lengths n*8][order n*4][expected n*20][sha1 n*20][md5 n*16][sha256 n*32][ok words]
+struct JobBuf {
+  size_t cap_n = 0;
+  uint8_t* h = nullptr;
+  uint8_t* d = nullptr;
+  size_t bytes = 0;
+  static size_t bytes_for(size_t n) { return align_up(n * (8 + 8 + 4 + 20 + 20 + 16 + 32) + ((n + 31) / 32) * 4 + 9 * 256, 256); }
+  size_t o_off(size_t) const { return 0; }
+  size_t o_len(size_t n) const { return align_up(n * 8, 256); }
+  size_t o_ord(size_t n) const { return o_len(n) + align_up(n * 8, 256); }
+  size_t o_exp(size_t n) const { return o_ord(n) + align_up(n * 4, 256); }
+  size_t o_sha1(size_t n) const { return o_exp(n) + align_up(n * 20, 256); }
+  size_t o_md5(size_t n) const { return o_sha1(n) + align_up(n * 20, 256); }
+  size_t o_sha256(size_t n) const { return o_md5(n) + align_up(n * 16, 256); }
+  size_t o_ok(size_t n) const { return o_sha256(n) + align_up(n * 32, 256); }
+  size_t o_end(size_t n) const { return o_ok(n) + align_up(((n + 31) / 32) * 4, 256); }
+};
+
+struct Slot {
+  uint64_t id = 0;
+  int gpu = 0;
+  size_t off = 0, bytes = 0;   // region of the ring
+  bool submitted = false;
+  bool done = false;           // ticket completed (or released) -> region reusable
+  uint64_t ticket = 0;
+};
+
+struct Ticket {
+  uint64_t id = 0;
+  int gpu = 0;
+  size_t n = 0;
+  uint32_t mask = 0;
+  bool has_expected = false;
+  bool finished = false;       // ev_done observed
+  bool timed = false;
+  int status = TH_OK;
+  JobBuf* jb = nullptr;
+  uint64_t slot_id = 0;        // 0 = device-resident submit
+  cudaEvent_t ev_done = nullptr;
+  cudaEvent_t ev_k0[3] = {nullptr, nullptr, nullptr}, ev_k1[3] = {nullptr, nullptr, nullptr};
+  th_done_cb cb = nullptr;
+  void* user = nullptr;
+  struct th_ctx* ctx = nullptr;
+};
+
+struct Gpu {
+  int dev = -1;
+  cudaStream_t s_copy = nullptr, s_alg[3] = {nullptr, nullptr, nullptr}, s_done = nullptr;
+  uint8_t* ring_h = nullptr;
+  uint8_t* ring_d = nullptr;
+  size_t ring_bytes = 0;
+  size_t head = 0, tail = 0;   // ring allocator: live region is [head, tail) modulo wrap
+  std::deque<Slot> slots;      // FIFO, oldest first
+  std::vector<JobBuf*> free_jobs;
+  th_stats st{};
+};
+
+}  // namespace
+
+struct th_ctx {
+  std::vector<Gpu> gpus;
+  std::mutex mu;
+  std::unordered_map<uint64_t, Ticket*> tickets;
+  uint64_t next_id = 1;
+  std::string last_error;
+  int sticky = TH_OK;
+};
+
+namespace {
+
+int cuda_fail(th_ctx* c, cudaError_t e, const char* what) {
+  c->last_error = std::string(what) + ": " + cudaGetErrorString(e);
+  c->sticky = TH_ECUDA;
+  return TH_ECUDA;
+}
+#define CU(ctx, call)                                             \
+  do {                                                            \
+    cudaError_t e__ = (call);                                     \
+    if (e__ != cudaSuccess) return cuda_fail((ctx), e__, #call);  \
+  } while (0)
+
+JobBuf* get_job(th_ctx* c, Gpu& g, size_t n, int* rc) {
+  for (size_t i = 0; i < g.free_jobs.size(); i++) {
+    if (g.free_jobs[i]->cap_n >= n) {
+      JobBuf* jb = g.free_jobs[i];
+      g.free_jobs.erase(g.free_jobs.begin() + (long)i);
+      return jb;
+    }
+  }
+  JobBuf* jb = new JobBuf();
+  jb->cap_n = std::max<size_t>(n, 1024);
+  jb->bytes = JobBuf::bytes_for(jb->cap_n);
+  cudaError_t e = cudaHostAlloc((void**)&jb->h, jb->bytes, cudaHostAllocPortable);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&jb->d, jb->bytes);
+  if (e != cudaSuccess) {
+    if (jb->h) cudaFreeHost(jb->h);
+    delete jb;
+    *rc = (e == cudaErrorMemoryAllocation) ? TH_ENOMEM : cuda_fail(c, e, "job buffer allocation");
+    return nullptr;
+  }
+  return jb;
+}
+
+// Marks finished tickets' slots reusable and advances the ring head over them.
+void reap(th_ctx* c, Gpu& g, bool block_on_oldest) {
+  for (auto& s : g.slots) {
+    if (s.done || !s.submitted) continue;
+    auto it = c->tickets.find(s.ticket);
+    if (it == c->tickets.end()) { s.done = true; continue; }
+    Ticket* t = it->second;
+    if (!t->finished) {
+      cudaError_t e = (block_on_oldest && &s == &g.slots.front()) ? cudaEventSynchronize(t->ev_done)
+                                                                  : cudaEventQuery(t->ev_done);
+      if (e == cudaSuccess) t->finished = true;
+      else if (e != cudaErrorNotReady) { t->finished = true; t->status = cuda_fail(c, e, "ticket event"); }
+    }
+    if (t->finished) s.done = true;
+  }
+  while (!g.slots.empty() && g.slots.front().done) {
+    g.slots.pop_front();
+    g.head = g.slots.empty() ? g.tail : g.slots.front().off;
+  }
+  if (g.slots.empty()) g.head = g.tail = 0;
+}
+
+void CUDART_CB host_done(void* p) {
+  Ticket* t = static_cast<Ticket*>(p);
+  if (t->cb) t->cb(t->user, t->id, TH_OK);
+}
+
+int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, size_t copy_off, size_t copy_bytes,
+            const th_msg* msgs, size_t n, uint32_t mask, const uint8_t* expected) {
+  JobBuf* jb = t->jb;
+  uint64_t* h_off = reinterpret_cast<uint64_t*>(jb->h + jb->o_off(n));
+  uint64_t* h_len = reinterpret_cast<uint64_t*>(jb->h + jb->o_len(n));
+  uint32_t* h_ord = reinterpret_cast<uint32_t*>(jb->h + jb->o_ord(n));
+  uint64_t total = 0;
+  bool uniform = true;
+  for (size_t i = 0; i < n; i++) {
+    h_off[i] = msgs[i].offset;
+    h_len[i] = msgs[i].length;
+    total += msgs[i].length;
+    uniform &= (msgs[i].length / 64 == msgs[0].length / 64);
+  }
+  // Length bucketing: a warp runs as long as its longest message, so lanes are dealt messages in
+  // descending block-count order (stable).  Equal-length batches keep the identity mapping.
+  const bool use_order = !uniform;
+  if (use_order) {
+    std::iota(h_ord, h_ord + n, 0u);
+    std::stable_sort(h_ord, h_ord + n, [&](uint32_t a, uint32_t b) { return h_len[a] / 64 > h_len[b] / 64; });
+  }
+  if (expected) std::memcpy(jb->h + jb->o_exp(n), expected, n * 20);
+
+  CU(c, cudaSetDevice(g.dev));
+  // H2D: payload (ring slot) then descriptors, one copy each.
+  if (copy_bytes) {
+    CU(c, cudaMemcpyAsync(g.ring_d + copy_off, g.ring_h + copy_off, copy_bytes, cudaMemcpyHostToDevice, g.s_copy));
+    g.st.h2d_bytes += copy_bytes;
+  }
+  const size_t desc_bytes = expected ? jb->o_sha1(n) : (use_order ? jb->o_exp(n) : jb->o_ord(n));
+  CU(c, cudaMemcpyAsync(jb->d, jb->h, desc_bytes, cudaMemcpyHostToDevice, g.s_copy));
+  g.st.h2d_bytes += desc_bytes;
+  cudaEvent_t ev_in;
+  CU(c, cudaEventCreateWithFlags(&ev_in, cudaEventDisableTiming));
+  CU(c, cudaEventRecord(ev_in, g.s_copy));
+
+  const uint64_t* d_off = reinterpret_cast<const uint64_t*>(jb->d + jb->o_off(n));
+  const uint64_t* d_len = reinterpret_cast<const uint64_t*>(jb->d + jb->o_len(n));
+  const uint32_t* d_ord = use_order ? reinterpret_cast<const uint32_t*>(jb->d + jb->o_ord(n)) : nullptr;
+  const size_t out_off[3] = {jb->o_sha1(n), jb->o_md5(n), jb->o_sha256(n)};
+  const size_t out_len[3] = {n * 20, n * 16, n * 32};
+  const size_t ok_bytes = ((n + 31) / 32) * 4;
+
+  for (int a = 0; a < 3; a++) {
+    if (!(mask & (1u << a))) continue;
+    cudaStream_t st = g.s_alg[a];
+    CU(c, cudaStreamWaitEvent(st, ev_in, 0));
+    int rc = TH_OK;
+    CU(c, cudaEventCreate(&t->ev_k0[a]));
+    CU(c, cudaEventCreate(&t->ev_k1[a]));
+    if (a == 0) {
+      uint32_t* d_ok = expected ? reinterpret_cast<uint32_t*>(jb->d + jb->o_ok(n)) : nullptr;
+      if (d_ok && use_order) CU(c, cudaMemsetAsync(d_ok, 0, ok_bytes, st));
+      CU(c, cudaEventRecord(t->ev_k0[a], st));
+      rc = th_sha1_batch(d_base, d_off, d_len, d_ord, 0, 0, (uint32_t)n, jb->d + out_off[0],
+                         expected ? jb->d + jb->o_exp(n) : nullptr, d_ok, st);
+    } else if (a == 1) {
+      CU(c, cudaEventRecord(t->ev_k0[a], st));
+      rc = th_md5_batch(d_base, d_off, d_len, d_ord, 0, 0, (uint32_t)n, jb->d + out_off[1], st);
+    } else {
+      CU(c, cudaEventRecord(t->ev_k0[a], st));
+      rc = th_sha256_batch(d_base, d_off, d_len, d_ord, 0, 0, (uint32_t)n, jb->d + out_off[2], st);
+    }
+    if (rc != TH_OK) {
+      if (rc == TH_ECUDA) return cuda_fail(c, cudaGetLastError(), "digest kernel launch");
+      return rc;
+    }
+    CU(c, cudaEventRecord(t->ev_k1[a], st));
+    g.st.launches += 1;
+    g.st.messages += n;
+    CU(c, cudaMemcpyAsync(jb->h + out_off[a], jb->d + out_off[a], out_len[a], cudaMemcpyDeviceToHost, st));
+    g.st.d2h_bytes += out_len[a];
+    if (a == 0 && expected) {
+      CU(c, cudaMemcpyAsync(jb->h + jb->o_ok(n), jb->d + jb->o_ok(n), ok_bytes, cudaMemcpyDeviceToHost, st));
+      g.st.d2h_bytes += ok_bytes;
+    }
+    cudaEvent_t ev_a;
+    CU(c, cudaEventCreateWithFlags(&ev_a, cudaEventDisableTiming));
+    CU(c, cudaEventRecord(ev_a, st));
+    CU(c, cudaStreamWaitEvent(g.s_done, ev_a, 0));
+    CU(c, cudaEventDestroy(ev_a));
+  }
+  CU(c, cudaEventDestroy(ev_in));
+  // the callback is enqueued before ev_done so that a ticket cannot be retired (th_result waits on
+  // ev_done) while its callback is still pending
+  if (t->cb) CU(c, cudaLaunchHostFunc(g.s_done, host_done, t));
+  CU(c, cudaEventCreateWithFlags(&t->ev_done, cudaEventDisableTiming));
+  CU(c, cudaEventRecord(t->ev_done, g.s_done));
+  g.st.bytes += total;
+  g.st.submits += 1;
+  return TH_OK;
+}
+
+int validate(const th_msg* msgs, size_t n, uint32_t mask, size_t limit) {
+  if (!msgs && n) return TH_EINVAL;
+  if (mask == 0 || (mask & ~7u)) return TH_EINVAL;
+  if (n == 0 || n > 0x7fffffffu) return TH_EINVAL;
+  for (size_t i = 0; i < n; i++) {
+    if (msgs[i].offset & 15) return TH_EALIGN;
+    if (msgs[i].length >= (1ull << 37)) return TH_ETOOBIG;
+    if (limit && (msgs[i].offset > limit || msgs[i].length > limit - msgs[i].offset)) return TH_EINVAL;
+  }
+  return TH_OK;
+}
+
+void free_ticket_events(Ticket* t) {
+  if (t->ev_done) cudaEventDestroy(t->ev_done);
+  for (int a = 0; a < 3; a++) {
+    if (t->ev_k0[a]) cudaEventDestroy(t->ev_k0[a]);
+    if (t->ev_k1[a]) cudaEventDestroy(t->ev_k1[a]);
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+int th_init(const int* gpu_ids, int n_gpus, size_t ring_bytes_per_gpu, th_ctx** out) {
+  if (!out || n_gpus <= 0) return TH_EINVAL;
+  *out = nullptr;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return TH_ENODEVICE;
+  th_ctx* c = new th_ctx();
+  c->gpus.resize((size_t)n_gpus);
+  for (int i = 0; i < n_gpus; i++) {
+    Gpu& g = c->gpus[(size_t)i];
+    g.dev = gpu_ids ? gpu_ids[i] : i;
+    cudaDeviceProp prop{};
+    if (g.dev < 0 || g.dev >= count || cudaGetDeviceProperties(&prop, g.dev) != cudaSuccess || prop.major < 10) {
+      th_shutdown(c);
+      return TH_ENODEVICE;  // kernels are sm_100a only; there is no other path
+    }
+    cudaError_t e = cudaSetDevice(g.dev);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&g.s_copy, cudaStreamNonBlocking);
+    for (int a = 0; a < 3 && e == cudaSuccess; a++) e = cudaStreamCreateWithFlags(&g.s_alg[a], cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&g.s_done, cudaStreamNonBlocking);
+    if (e == cudaSuccess && ring_bytes_per_gpu) {
+      g.ring_bytes = align_up(ring_bytes_per_gpu, kRingAlign);
+      e = cudaHostAlloc((void**)&g.ring_h, g.ring_bytes, cudaHostAllocPortable);
+      if (e == cudaSuccess) e = cudaMalloc((void**)&g.ring_d, g.ring_bytes);
+    }
+    if (e != cudaSuccess) {
+      int rc = (e == cudaErrorMemoryAllocation) ? TH_ENOMEM : TH_ECUDA;
+      th_shutdown(c);
+      return rc;
+    }
+  }
+  *out = c;
+  return TH_OK;
+}
+
+int th_shutdown(th_ctx* c) {
+  if (!c) return TH_EINVAL;
+  for (auto& g : c->gpus) {
+    if (g.dev < 0) continue;
+    cudaSetDevice(g.dev);
+    cudaDeviceSynchronize();
+    for (auto* jb : g.free_jobs) { cudaFreeHost(jb->h); cudaFree(jb->d); delete jb; }
+    if (g.ring_h) cudaFreeHost(g.ring_h);
+    if (g.ring_d) cudaFree(g.ring_d);
+    if (g.s_copy) cudaStreamDestroy(g.s_copy);
+    for (auto& s : g.s_alg) if (s) cudaStreamDestroy(s);
+    if (g.s_done) cudaStreamDestroy(g.s_done);
+  }
+  for (auto& kv : c->tickets) {
+    Ticket* t = kv.second;
+    free_ticket_events(t);
+    if (t->jb) { cudaFreeHost(t->jb->h); cudaFree(t->jb->d); delete t->jb; }
+    delete t;
+  }
+  delete c;
+  return TH_OK;
+}
+
+int th_gpu_count(const th_ctx* c) { return c ? (int)c->gpus.size() : TH_EINVAL; }
+
+int th_ring_acquire(th_ctx* c, int gpu, size_t bytes, void** host_ptr, th_slot* slot) {
+  if (!c || !host_ptr || !slot || gpu < 0 || gpu >= (int)c->gpus.size() || bytes == 0) return TH_EINVAL;
+  std::lock_guard<std::mutex> lk(c->mu);
+  if (c->sticky) return c->sticky;
+  Gpu& g = c->gpus[(size_t)gpu];
+  const size_t need = align_up(bytes, kRingAlign);
+  if (need > g.ring_bytes) return TH_ETOOBIG;
+  cudaSetDevice(g.dev);
+  for (;;) {
+    reap(c, g, false);
+    size_t off = (size_t)-1;
+    if (g.slots.empty()) {
+      off = 0;
+    } else if (g.tail >= g.head && g.tail != g.head) {  // live region does not wrap
+      if (g.ring_bytes - g.tail >= need) off = g.tail;
+      else if (g.head >= need) off = 0;
+    } else if (g.tail < g.head) {                       // wrapped: free gap is [tail, head)
+      if (g.head - g.tail >= need) off = g.tail;
+    }
+    if (off != (size_t)-1) {
+      Slot s;
+      s.id = c->next_id++;
+      s.gpu = gpu;
+      s.off = off;
+      s.bytes = need;
+      if (g.slots.empty()) g.head = off;
+      g.tail = off + need;
+      g.slots.push_back(s);
+      *host_ptr = g.ring_h + off;
+      *slot = s.id;
+      return TH_OK;
+    }
+    // full: wait for the oldest slot's ticket
+    if (!g.slots.front().submitted) return TH_EBUSY;
+    reap(c, g, true);
+    if (c->sticky) return c->sticky;
+  }
+}
+
+int th_ring_release(th_ctx* c, th_slot slot) {
+  if (!c) return TH_EINVAL;
+  std::lock_guard<std::mutex> lk(c->mu);
+  for (auto& g : c->gpus)
+    for (auto& s : g.slots)
+      if (s.id == slot) {
+        if (s.submitted) return TH_ESTATE;
+        s.done = true;
+        reap(c, g, false);
+        return TH_OK;
+      }
+  return TH_ESTATE;
+}
+
+static int submit_common(th_ctx* c, int gpu, Slot* slot, const void* d_base_user, const th_msg* msgs, size_t n,
+                         uint32_t mask, const uint8_t* expected, th_done_cb cb, void* user, th_ticket* out) {
+  Gpu& g = c->gpus[(size_t)gpu];
+  int rc = TH_OK;
+  cudaSetDevice(g.dev);
+  JobBuf* jb = get_job(c, g, n, &rc);
+  if (!jb) return rc;
+  Ticket* t = new Ticket();
+  t->id = c->next_id++;
+  t->gpu = gpu;
+  t->n = n;
+  t->mask = mask;
+  t->has_expected = expected != nullptr && (mask & TH_ALG_SHA1);
+  t->jb = jb;
+  t->cb = cb;
+  t->user = user;
+  t->ctx = c;
+  const uint8_t* d_base = slot ? g.ring_d + slot->off : static_cast<const uint8_t*>(d_base_user);
+  size_t used = 0;
+  if (slot) {
+    for (size_t i = 0; i < n; i++) used = std::max<size_t>(used, (size_t)(msgs[i].offset + msgs[i].length));
+    used = align_up(used, 16);
+    t->slot_id = slot->id;
+  }
+  rc = enqueue(c, g, t, d_base, slot ? slot->off : 0, used, msgs, n, mask, t->has_expected ? expected : nullptr);
+  if (rc != TH_OK) {
+    free_ticket_events(t);
+    g.free_jobs.push_back(jb);
+    delete t;
+    return rc;
+  }
+  if (slot) { slot->submitted = true; slot->ticket = t->id; }
+  c->tickets[t->id] = t;
+  *out = t->id;
+  return TH_OK;
+}
+
+int th_submit(th_ctx* c, th_slot slot_id, const th_msg* msgs, size_t n, uint32_t mask, const uint8_t* expected,
+              th_done_cb cb, void* user, th_ticket* out) {
+  if (!c || !out) return TH_EINVAL;
+  std::lock_guard<std::mutex> lk(c->mu);
+  if (c->sticky) return c->sticky;
+  for (size_t gi = 0; gi < c->gpus.size(); gi++)
+    for (auto& s : c->gpus[gi].slots)
+      if (s.id == slot_id) {
+        if (s.submitted || s.done) return TH_ESTATE;
+        int rc = validate(msgs, n, mask, s.bytes);
+        if (rc != TH_OK) return rc;
+        return submit_common(c, (int)gi, &s, nullptr, msgs, n, mask, expected, cb, user, out);
+      }
+  return TH_ESTATE;
+}
+
+int th_submit_device(th_ctx* c, int gpu, const void* d_base, const th_msg* msgs, size_t n, uint32_t mask,
+                     const uint8_t* expected, th_done_cb cb, void* user, th_ticket* out) {
+  if (!c || !out || gpu < 0 || gpu >= (int)c->gpus.size()) return TH_EINVAL;
+  if (reinterpret_cast<uintptr_t>(d_base) & 15) return TH_EALIGN;
+  std::lock_guard<std::mutex> lk(c->mu);
+  if (c->sticky) return c->sticky;
+  int rc = validate(msgs, n, mask, 0);
+  if (rc != TH_OK) return rc;
+  if (!d_base) return TH_EINVAL;
+  return submit_common(c, gpu, nullptr, d_base, msgs, n, mask, expected, cb, user, out);
+}
+
+static int wait_locked(th_ctx* c, Ticket* t) {
+  if (!t->finished) {
+    cudaSetDevice(c->gpus[(size_t)t->gpu].dev);
+    cudaError_t e = cudaEventSynchronize(t->ev_done);
+    t->finished = true;
+    if (e != cudaSuccess) t->status = cuda_fail(c, e, "cudaEventSynchronize(ticket)");
+  }
+  if (!t->timed && t->status == TH_OK) {
+    for (int a = 0; a < 3; a++) {
+      float ms = 0.f;
+      if (t->ev_k0[a] && cudaEventElapsedTime(&ms, t->ev_k0[a], t->ev_k1[a]) == cudaSuccess)
+        c->gpus[(size_t)t->gpu].st.kernel_ms += ms;
+    }
+    t->timed = true;
+  }
+  return t->status;
+}
+
+int th_wait(th_ctx* c, th_ticket id) {
+  if (!c) return TH_EINVAL;
+  std::lock_guard<std::mutex> lk(c->mu);
+  auto it = c->tickets.find(id);
+  if (it == c->tickets.end()) return TH_ESTATE;
+  return wait_locked(c, it->second);
+}
+
+int th_result(th_ctx* c, th_ticket id, uint8_t* sha1, uint8_t* md5, uint8_t* sha256, uint32_t* ok_bits) {
+  if (!c) return TH_EINVAL;
+  std::lock_guard<std::mutex> lk(c->mu);
+  auto it = c->tickets.find(id);
+  if (it == c->tickets.end()) return TH_ESTATE;
+  Ticket* t = it->second;
+  int rc = wait_locked(c, t);
+  const size_t n = t->n;
+  JobBuf* jb = t->jb;
+  if (rc == TH_OK) {
+    if (sha1) { if (!(t->mask & TH_ALG_SHA1)) rc = TH_EINVAL; else std::memcpy(sha1, jb->h + jb->o_sha1(n), n * 20); }
+    if (md5) { if (!(t->mask & TH_ALG_MD5)) rc = TH_EINVAL; else std::memcpy(md5, jb->h + jb->o_md5(n), n * 16); }
+    if (sha256) { if (!(t->mask & TH_ALG_SHA256)) rc = TH_EINVAL; else std::memcpy(sha256, jb->h + jb->o_sha256(n), n * 32); }
+    if (ok_bits) { if (!t->has_expected) rc = TH_EINVAL; else std::memcpy(ok_bits, jb->h + jb->o_ok(n), ((n + 31) / 32) * 4); }
+  }
+  Gpu& g = c->gpus[(size_t)t->gpu];
+  if (t->slot_id)
+    for (auto& s : g.slots)
+      if (s.id == t->slot_id) s.done = true;
+  free_ticket_events(t);
+  g.free_jobs.push_back(jb);
+  c->tickets.erase(it);
+  delete t;
+  reap(c, g, false);
+  return rc;
+}
+
+int th_etag_combine(th_ctx* c, int gpu, const uint8_t* md5s, const uint32_t* counts, size_t n_objects,
+                    uint8_t* out16) {
+  if (!c || gpu < 0 || gpu >= (int)c->gpus.size() || !counts || !out16 || n_objects > 0x7fffffffu) return TH_EINVAL;
+  if (n_objects == 0) return TH_OK;
+  std::lock_guard<std::mutex> lk(c->mu);
+  if (c->sticky) return c->sticky;
+  Gpu& g = c->gpus[(size_t)gpu];
+  CU(c, cudaSetDevice(g.dev));
+  std::vector<uint64_t> prefix(n_objects + 1, 0);
+  for (size_t i = 0; i < n_objects; i++) prefix[i + 1] = prefix[i] + counts[i];
+  const size_t parts = (size_t)prefix[n_objects];
+  if (parts && !md5s) return TH_EINVAL;
+  const size_t b_md5 = align_up(parts * 16 + 16, 256), b_pre = align_up((n_objects + 1) * 8, 256), b_out = n_objects * 16;
+  uint8_t* d = nullptr;
+  CU(c, cudaMalloc((void**)&d, b_md5 + b_pre + b_out));
+  cudaStream_t st = g.s_alg[1];
+  cudaError_t e = cudaSuccess;
+  if (parts) e = cudaMemcpyAsync(d, md5s, parts * 16, cudaMemcpyHostToDevice, st);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(d + b_md5, prefix.data(), (n_objects + 1) * 8, cudaMemcpyHostToDevice, st);
+  int rc = TH_OK;
+  if (e == cudaSuccess) rc = th_etag_combine_device(d, reinterpret_cast<uint64_t*>(d + b_md5), (uint32_t)n_objects, d + b_md5 + b_pre, st);
+  if (e == cudaSuccess && rc == TH_OK) e = cudaMemcpyAsync(out16, d + b_md5 + b_pre, b_out, cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFree(d);
+  if (e != cudaSuccess) return cuda_fail(c, e, "th_etag_combine");
+  if (rc == TH_OK) {
+    g.st.launches += 1;
+    g.st.h2d_bytes += parts * 16 + (n_objects + 1) * 8;
+    g.st.d2h_bytes += b_out;
+  }
+  return rc;
+}
+
+int th_stats_get(th_ctx* c, int gpu, th_stats* out) {
+  if (!c || !out || gpu >= (int)c->gpus.size()) return TH_EINVAL;
+  std::lock_guard<std::mutex> lk(c->mu);
+  std::memset(out, 0, sizeof(*out));
+  for (size_t i = 0; i < c->gpus.size(); i++) {
+    if (gpu >= 0 && (int)i != gpu) continue;
+    const th_stats& s = c->gpus[i].st;
+    out->messages += s.messages; out->bytes += s.bytes; out->launches += s.launches;
+    out->h2d_bytes += s.h2d_bytes; out->d2h_bytes += s.d2h_bytes; out->submits += s.submits;
+    out->kernel_ms += s.kernel_ms;
+  }
+  return TH_OK;
+}
+
+const char* th_strerror(int code) {
+  switch (code) {
+    case TH_OK: return "ok";
+    case TH_EINVAL: return "invalid argument";
+    case TH_ENODEVICE: return "no usable CUDA device (sm_100 required; there is no CPU fallback)";
+    case TH_ECUDA: return "CUDA runtime error (see th_last_error)";
+    case TH_ENOMEM: return "out of host or device memory";
+    case TH_EALIGN: return "message offset or base pointer is not 16-byte aligned";
+    case TH_EBUSY: return "ring full and its oldest slot has not been submitted";
+    case TH_ETOOBIG: return "request exceeds the ring size or a fixed limit";
+    case TH_ESTATE: return "unknown ticket/slot or call out of order";
+    default: return "unknown error";
+  }
+}
+
+const char* th_last_error(const th_ctx* c) { return c ? c->last_error.c_str() : ""; }
+
+void th_hex(const uint8_t* in, size_t n, char* out) {
+  static const char d[] = "0123456789abcdef";
+  for (size_t i = 0; i < n; i++) { out[2 * i] = d[in[i] >> 4]; out[2 * i + 1] = d[in[i] & 15]; }
+  out[2 * n] = 0;
+}
+
+size_t th_base64(const uint8_t* in, size_t n, char* out) {
+  static const char a[] = "ABCDEFGHIJKLMNOPQRSTUVWXYZabcdefghijklmnopqrstuvwxyz0123456789+/";
+  size_t o = 0;
+  for (size_t i = 0; i + 2 < n; i += 3) {
+    const uint32_t v = ((uint32_t)in[i] << 16) | ((uint32_t)in[i + 1] << 8) | in[i + 2];
+    out[o++] = a[v >> 18]; out[o++] = a[(v >> 12) & 63]; out[o++] = a[(v >> 6) & 63]; out[o++] = a[v & 63];
+  }
+  const size_t rem = n % 3;
+  if (rem == 1) {
+    const uint32_t v = (uint32_t)in[n - 1] << 4;
+    out[o++] = a[v >> 6]; out[o++] = a[v & 63]; out[o++] = '='; out[o++] = '=';
+  } else if (rem == 2) {
+    const uint32_t v = (((uint32_t)in[n - 2] << 8) | in[n - 1]) << 2;
+    out[o++] = a[v >> 12]; out[o++] = a[(v >> 6) & 63]; out[o++] = a[v & 63]; out[o++] = '=';
+  }
+  out[o] = 0;
+  return o;
+}
+
+}  // extern "C"

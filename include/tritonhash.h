@@ -1,0 +1,160 @@
+/*
+ * tritonhash.h — C ABI of the B200 byte-integrity engine (libtritonhash.so).
+ *
+ * Drop-in boundary for the one data-parallel path of tritonmedia/downloader: the digests its
+ * dependencies compute through Node crypto, batched as thousands of independent messages.
+ * Each entry point cites the reference interface it replaces (paths are in the reference tree;
+ * [dep] = behaviour of the pinned, un-vendored npm dependency).
+ *
+ * Conventions
+ *   - plain C, no C++ types, no exceptions; every call returns int: 0 = TH_OK, < 0 = TH_E*.
+ *   - a digest MISMATCH is data (ok_bits), never an error ([dep] webtorrent re-requests the piece).
+ *   - there is NO CPU fallback: without a usable GPU th_init fails with TH_ENODEVICE.
+ *   - digests are raw bytes in the standard byte order (what crypto's .digest() Buffer holds):
+ *     SHA-1 20 B, MD5 16 B, SHA-256 32 B.  hex / base64 are th_hex / th_base64.
+ *   - message start addresses must be 16-byte aligned on the device (TH_EALIGN otherwise): the
+ *     kernels stage each lane's message with 1-D bulk async copies (cp.async.bulk).
+ */
+#ifndef TRITONHASH_H
+#define TRITONHASH_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TH_ALG_SHA1 1u   /* crypto.createHash('sha1')   — [dep] simple-sha1@2.1.2, webtorrent@0.107.6 */
+#define TH_ALG_MD5 2u    /* crypto.createHash('md5')    — [dep] minio@7.0.12 getHashSummer(false)    */
+#define TH_ALG_SHA256 4u /* crypto.createHash('sha256') — [dep] minio@7.0.12 getHashSummer(true)     */
+
+enum {
+  TH_OK = 0,
+  TH_EINVAL = -1,    /* bad argument */
+  TH_ENODEVICE = -2, /* no CUDA device / not sm_100 capable; product has no CPU path */
+  TH_ECUDA = -3,     /* CUDA runtime error (sticky per context; text via th_last_error) */
+  TH_ENOMEM = -4,    /* host or device allocation failed */
+  TH_EALIGN = -5,    /* message offset / base pointer not 16-byte aligned */
+  TH_EBUSY = -6,     /* ring full and the oldest slot has not been submitted yet */
+  TH_ETOOBIG = -7,   /* request larger than the ring / a fixed limit */
+  TH_ESTATE = -8     /* unknown ticket / slot, or call out of order */
+};
+
+typedef struct th_ctx th_ctx;
+typedef uint64_t th_ticket;
+typedef uint64_t th_slot;
+
+/* One message = bytes [offset, offset+length) of the batch buffer (a ring slot or a device base).
+ * Replaces: one piece Buffer handed to sha1(buf, cb) ([dep] webtorrent lib/torrent.js; call site
+ * lib/download.js:64-66) or one part range [start,end] streamed into getHashSummer ([dep] minio
+ * fPutObject; call site lib/upload.js:45). */
+typedef struct th_msg {
+  uint64_t offset; /* multiple of 16 */
+  uint64_t length; /* any value, 0 .. 2^61 */
+} th_msg;
+
+typedef struct th_stats {
+  uint64_t messages;    /* messages hashed (per requested digest) */
+  uint64_t bytes;       /* message bytes hashed, counted once per message per submit */
+  uint64_t launches;    /* kernels launched by this library */
+  uint64_t h2d_bytes;   /* bytes copied host -> device (payload + descriptors) */
+  uint64_t d2h_bytes;   /* bytes copied device -> host (digests, ok words) */
+  uint64_t submits;
+  double kernel_ms;     /* summed device time of digest kernels (from CUDA events) */
+} th_stats;
+
+/* Completion callback, delivered on a library (CUDA host-callback) thread — the N-API shim
+ * forwards it with a napi_threadsafe_function.  status is TH_OK or TH_ECUDA. */
+typedef void (*th_done_cb)(void* user, th_ticket ticket, int status);
+
+/* ---- context ------------------------------------------------------------------------------
+ * Replaces nothing in the reference (Node's crypto needs no set-up); owns, per GPU, a pinned host
+ * ring + its device mirror, the copy / compute streams and the descriptor staging buffers.
+ * gpu_ids == NULL -> devices 0..n_gpus-1.  ring_bytes_per_gpu may be 0 (device-resident use only). */
+int th_init(const int* gpu_ids, int n_gpus, size_t ring_bytes_per_gpu, th_ctx** out);
+int th_shutdown(th_ctx* ctx);
+int th_gpu_count(const th_ctx* ctx);
+
+/* ---- host path: pinned ring -> H2D -> digest kernels -> D2H digests -------------------------
+ * th_ring_acquire hands out `bytes` of pinned host memory the caller fills (fs.read target —
+ * replaces the GC-owned piece/part Buffers of [dep] webtorrent / minio).  Blocks while the ring is
+ * full of in-flight slots; the slot returns to the ring when its ticket completes. */
+int th_ring_acquire(th_ctx* ctx, int gpu, size_t bytes, void** host_ptr, th_slot* slot);
+/* Drops a slot that was acquired but will not be submitted. */
+int th_ring_release(th_ctx* ctx, th_slot slot);
+
+/* Non-blocking.  Hashes msgs[0..n) of the slot with every digest in alg_mask.
+ * expected_sha1 (nullable, n*20 raw bytes = info.pieces of the .torrent, [dep] parse-torrent@7.0.0)
+ * enables the fused compare: bit i of ok_bits = (sha1(msg i) == expected i), which is webtorrent's
+ * `hash === this._hashes[index]` -> bitfield.set(index) ([dep] lib/torrent.js). */
+int th_submit(th_ctx* ctx, th_slot slot, const th_msg* msgs, size_t n, uint32_t alg_mask,
+              const uint8_t* expected_sha1, th_done_cb cb, void* user, th_ticket* out);
+
+/* Same, for data already resident on `gpu` (benchmarks, chained GPU stages).  d_base is a device
+ * pointer (16-byte aligned); offsets in msgs are relative to it.  The caller keeps d_base alive
+ * until the ticket completes. */
+int th_submit_device(th_ctx* ctx, int gpu, const void* d_base, const th_msg* msgs, size_t n,
+                     uint32_t alg_mask, const uint8_t* expected_sha1, th_done_cb cb, void* user,
+                     th_ticket* out);
+
+/* Blocks until the ticket's digests are in host memory. */
+int th_wait(th_ctx* ctx, th_ticket ticket);
+/* Copies results out (any pointer may be NULL) and retires the ticket.  Waits if needed.
+ * sha1: n*20, md5: n*16, sha256: n*32, ok_bits: ceil(n/32) words, bit (i&31) of word i>>5. */
+int th_result(th_ctx* ctx, th_ticket ticket, uint8_t* sha1, uint8_t* md5, uint8_t* sha256,
+              uint32_t* ok_bits);
+
+/* Multipart object ETag: out16[j] = md5(md5s of object j's parts, concatenated), computed on the
+ * GPU by one warp per object (message words travel by warp shuffle).  counts[j] = parts of object j,
+ * md5s = all part digests back to back (host memory).  The S3 ETag string is hex(out16)+"-"+count.
+ * Replaces the ETag the S3 server returns to [dep] minio completeMultipartUpload (lib/upload.js:45). */
+int th_etag_combine(th_ctx* ctx, int gpu, const uint8_t* md5s, const uint32_t* counts,
+                    size_t n_objects, uint8_t* out16);
+
+int th_stats_get(th_ctx* ctx, int gpu /* -1 = sum over GPUs */, th_stats* out);
+const char* th_strerror(int code);
+/* Text of the last CUDA error seen by this context ("" if none). */
+const char* th_last_error(const th_ctx* ctx);
+
+/* ---- encoders ([dep] minio getHashSummer emits base64(md5) and lower-case hex(sha256);
+ *      simple-sha1 emits lower-case hex) -------------------------------------------------------- */
+void th_hex(const uint8_t* in, size_t n, char* out /* 2n+1 */);
+size_t th_base64(const uint8_t* in, size_t n, char* out /* 4*ceil(n/3)+1 */);
+
+/* ---- launch-level API: device pointers in, device pointers out, caller's stream ---------------
+ * No context, no allocation, no synchronisation: exactly one kernel launch on `stream`
+ * (a cudaStream_t; NULL = default stream) of the current device.  These are what th_submit*
+ * launch; benchmarks time them with CUDA events on that stream.
+ *   message i = d_base + (d_offsets ? d_offsets[i] : i*stride), length d_lengths ? d_lengths[i] : len.
+ *   d_order (nullable): thread slot k hashes message d_order[k] (host-side length bucketing);
+ *   with d_order the caller zeroes d_ok_bits first.
+ * Replaces: th_sha1_batch -> sha1(buf) per piece + compare ([dep] webtorrent _verifyPieces / onChunk);
+ *           th_md5_batch / th_sha256_batch -> getHashSummer per part ([dep] minio fPutObject). */
+int th_sha1_batch(const void* d_base, const uint64_t* d_offsets, const uint64_t* d_lengths,
+                  const uint32_t* d_order, uint64_t stride, uint64_t len, uint32_t n,
+                  uint8_t* d_out20, const uint8_t* d_expected20, uint32_t* d_ok_bits, void* stream);
+int th_md5_batch(const void* d_base, const uint64_t* d_offsets, const uint64_t* d_lengths,
+                 const uint32_t* d_order, uint64_t stride, uint64_t len, uint32_t n,
+                 uint8_t* d_out16, void* stream);
+int th_sha256_batch(const void* d_base, const uint64_t* d_offsets, const uint64_t* d_lengths,
+                    const uint32_t* d_order, uint64_t stride, uint64_t len, uint32_t n,
+                    uint8_t* d_out32, void* stream);
+/* d_part_prefix: n_objects+1 exclusive prefix sums of part counts (device). */
+int th_etag_combine_device(const uint8_t* d_md5s, const uint64_t* d_part_prefix, uint32_t n_objects,
+                           uint8_t* d_out16, void* stream);
+/* Synthetic data: 64-bit word j of message i = splitmix64(seed + (i<<40) + j), LE.
+ * Fills n messages of `len` bytes at d_dst + k*stride for message index first_msg+k. */
+int th_synth_fill(void* d_dst, uint64_t first_msg, uint64_t n, uint64_t len, uint64_t stride,
+                  uint64_t seed, void* stream);
+
+/* Staging geometry of the digest kernels: bytes each lane stages per pipeline stage (multiple of
+ * 64, 64..1024) and the number of stages (2..4).  Process-wide; returns TH_EINVAL if no such
+ * variant was compiled.  Defaults are the tuned values in DESIGN.md. */
+int th_set_staging(uint32_t alg, int chunk_bytes, int stages);
+int th_get_staging(uint32_t alg, int* chunk_bytes, int* stages);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TRITONHASH_H */

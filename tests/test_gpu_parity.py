@@ -1,0 +1,282 @@
+"""GPU parity tests: every digest that leaves the CUDA path, through the C ABI, must be bit-exact
+with the CPU oracle (oracle/: plain-C restatement + libcrypto, pinned by tests/golden/kat.json)."""
+import ctypes as C
+import hashlib
+
+import numpy as np
+import pytest
+
+import oracle
+from conftest import kat_message
+
+pytestmark = pytest.mark.gpu
+
+SHA1, MD5, SHA256 = 1, 2, 4
+ALL = SHA1 | MD5 | SHA256
+NAMES = {SHA1: "sha1", MD5: "md5", SHA256: "sha256"}
+VARIANTS = [(64, 4), (128, 2), (128, 3), (128, 4), (256, 2), (256, 3), (512, 2)]
+
+
+@pytest.fixture(scope="module")
+def torch():
+    import torch
+    assert torch.cuda.is_available(), "-m gpu tests need a GPU"
+    torch.cuda.set_device(0)
+    return torch
+
+
+@pytest.fixture(scope="module")
+def eng(torch):
+    from downloader_b200 import Engine
+    e = Engine([0], ring_bytes=192 << 20)
+    yield e
+    e.close()
+
+
+@pytest.fixture(scope="module")
+def L():
+    from downloader_b200 import _capi
+    return _capi.lib()
+
+
+def ref_digests(alg, bufs):
+    return np.stack([np.frombuffer(hashlib.new(NAMES[alg], bytes(b)).digest(), np.uint8) for b in bufs])
+
+
+def test_kat_vectors(eng, kat):
+    msgs = [kat_message(v) for v in kat["vectors"]]
+    out = eng.hash_batch(msgs, ALL)
+    for i, v in enumerate(kat["vectors"]):
+        for alg in (SHA1, MD5, SHA256):
+            assert out[alg][i].tobytes().hex() == v[NAMES[alg]], (NAMES[alg], i)
+
+
+def boundary_lengths():
+    lens = list(range(0, 258))
+    for k in range(8, 21):
+        lens += [(1 << k) - 1, 1 << k, (1 << k) + 1]
+    lens += [55, 56, 63, 64, 65, 119, 120, 4096 - 9, 4096 - 8, 65536 + 55, 65536 + 56]
+    return lens
+
+
+@pytest.mark.parametrize("alg", [SHA1, MD5, SHA256])
+def test_every_boundary_length_vs_oracle(eng, alg):
+    lens = boundary_lengths()
+    rng = np.random.default_rng(5)
+    bufs = [rng.integers(0, 256, n, dtype=np.uint8) for n in lens]
+    out = eng.hash_batch(bufs, alg)[alg]
+    # oracle = plain-C restatement over the same bytes; hashlib (OpenSSL) as a second witness
+    flat = np.concatenate(bufs) if bufs else np.zeros(0, np.uint8)
+    off = np.cumsum([0] + lens[:-1]).astype(np.uint64)
+    exp = oracle.batch(alg, flat, off, np.array(lens, np.uint64), threads=4)
+    bad = np.nonzero((out != exp).any(axis=1))[0]
+    assert bad.size == 0, f"{NAMES[alg]} mismatch at lengths {[lens[i] for i in bad[:10]]}"
+    assert (exp == ref_digests(alg, bufs)).all()
+
+
+@pytest.mark.parametrize("ch,nst", VARIANTS)
+def test_all_staging_variants(eng, L, ch, nst):
+    ch0, st0 = C.c_int(), C.c_int()
+    L.th_get_staging(1, C.byref(ch0), C.byref(st0))
+    try:
+        assert L.th_set_staging(7, ch, nst) == 0
+        lens = [0, 1, 15, 16, 17, 55, 56, 63, 64, 65, ch - 1, ch, ch + 1, ch + 55, ch + 56, 2 * ch, 3 * ch + 63,
+                nst * ch, nst * ch + 1, (nst + 1) * ch - 8, 5000, 70001] + list(range(1000, 1040))
+        bufs = [oracle.synth(i, n) for i, n in enumerate(lens)]
+        out = eng.hash_batch(bufs, ALL)
+        for alg in (SHA1, MD5, SHA256):
+            assert (out[alg] == ref_digests(alg, bufs)).all(), (NAMES[alg], ch, nst)
+    finally:
+        assert L.th_set_staging(7, ch0.value, st0.value) == 0
+
+
+def test_synth_fill_matches_oracle_generator(torch, L):
+    n, ln, stride = 37, 1003, 1008
+    d = torch.zeros(n * stride, dtype=torch.uint8, device="cuda")
+    assert L.th_synth_fill(d.data_ptr(), 5, n, ln, stride, oracle.DEFAULT_SEED, None) == 0
+    torch.cuda.synchronize()
+    h = d.cpu().numpy()
+    for k in range(n):
+        assert (h[k * stride:k * stride + ln] == oracle.synth(5 + k, ln)).all()
+        assert (h[k * stride + ln:(k + 1) * stride] == 0).all()
+
+
+@pytest.mark.parametrize("n,ln", [(1, 64), (33, 4096), (1000, 16384), (4096, 262144), (7, 16 << 20)])
+def test_launch_level_uniform_batches(torch, L, n, ln):
+    """Device-resident, stride-addressed launch (the shape of BASELINE configs 2 and 3)."""
+    d = torch.empty(n * ln, dtype=torch.uint8, device="cuda")
+    assert L.th_synth_fill(d.data_ptr(), 0, n, ln, ln, oracle.DEFAULT_SEED, None) == 0
+    outs = {a: torch.zeros(n * oracle.DIGEST_LEN[a], dtype=torch.uint8, device="cuda") for a in (SHA1, MD5, SHA256)}
+    assert L.th_sha1_batch(d.data_ptr(), None, None, None, ln, ln, n, outs[SHA1].data_ptr(), None, None, None) == 0
+    assert L.th_md5_batch(d.data_ptr(), None, None, None, ln, ln, n, outs[MD5].data_ptr(), None) == 0
+    assert L.th_sha256_batch(d.data_ptr(), None, None, None, ln, ln, n, outs[SHA256].data_ptr(), None) == 0
+    torch.cuda.synchronize()
+    # oracle on a bounded sample of messages, regenerated on the host from the generator definition
+    pick = sorted(set(np.linspace(0, n - 1, min(n, 48)).astype(int).tolist()))
+    host = np.concatenate([oracle.synth(i, ln) for i in pick])
+    off = (np.arange(len(pick)) * ln).astype(np.uint64)
+    lens = np.full(len(pick), ln, np.uint64)
+    for a in (SHA1, MD5, SHA256):
+        got = outs[a].cpu().numpy().reshape(n, -1)[pick]
+        _, exp = oracle.evp_batch(a, host, off, lens, threads=8)
+        assert (got == exp[a]).all(), NAMES[a]
+        assert (oracle.batch(a, host, off, lens, threads=8) == exp[a]).all()
+
+
+def test_fused_verify_bitfield_identity_order(torch, L):
+    """webtorrent's `hash === _hashes[i]` -> bitfield, fused into the SHA-1 kernel (uniform batch)."""
+    n, ln = 2000, 16384
+    d = torch.empty(n * ln, dtype=torch.uint8, device="cuda")
+    L.th_synth_fill(d.data_ptr(), 0, n, ln, ln, 7, None)
+    out = torch.zeros(n * 20, dtype=torch.uint8, device="cuda")
+    assert L.th_sha1_batch(d.data_ptr(), None, None, None, ln, ln, n, out.data_ptr(), None, None, None) == 0
+    exp = out.clone()
+    bad = [0, 31, 32, 777, 1999]
+    e2 = exp.view(n, 20)
+    for b in bad:
+        e2[b, (b * 7) % 20] ^= 0x40
+    ok = torch.full(((n + 31) // 32,), -1, dtype=torch.int32, device="cuda")
+    assert L.th_sha1_batch(d.data_ptr(), None, None, None, ln, ln, n, out.data_ptr(), exp.data_ptr(), ok.data_ptr(), None) == 0
+    torch.cuda.synchronize()
+    words = ok.cpu().numpy().view(np.uint32)
+    bits = ((words[np.arange(n) >> 5] >> (np.arange(n) & 31)) & 1).astype(bool)
+    assert sorted(np.nonzero(~bits)[0].tolist()) == bad
+    # bits past n in the last word are zero
+    assert (int(words[-1]) >> (n & 31)) == 0 if n & 31 else True
+    # and the digests themselves are right
+    host = oracle.synth_batch(0, 8, ln, seed=7)
+    o8 = oracle.batch(SHA1, host, np.arange(8, dtype=np.uint64) * ln, np.full(8, ln, np.uint64))
+    assert (out.cpu().numpy().reshape(n, 20)[:8] == o8).all()
+
+
+def test_fused_verify_through_submit_mixed_lengths(eng):
+    """Same through th_submit with ragged pieces (short last piece) -> length-bucketed order path."""
+    rng = np.random.default_rng(3)
+    lens = [262144] * 40 + [1000, 0, 64, 262144 - 1, 77777] + [16384] * 30
+    bufs = [rng.integers(0, 256, n, dtype=np.uint8) for n in lens]
+    exp = ref_digests(SHA1, bufs).copy()
+    bad = [2, 41, 44, 74]
+    for b in bad:
+        exp[b, 19] ^= 1
+    out = eng.hash_batch(bufs, SHA1 | MD5, expected_sha1=exp)
+    assert sorted(np.nonzero(~out["ok"])[0].tolist()) == bad
+    assert (out[SHA1] == ref_digests(SHA1, bufs)).all()
+    assert (out[MD5] == ref_digests(MD5, bufs)).all()
+
+
+def test_etag_combine_vs_oracle(eng, kat):
+    rng = np.random.default_rng(9)
+    counts = [1, 2, 3, 4, 5, 7, 8, 9, 64, 1000, 10000, 0]
+    md5s = rng.integers(0, 256, (sum(counts), 16), dtype=np.uint8)
+    out = eng.etag_combine(md5s, counts)
+    pos = 0
+    for j, c in enumerate(counts):
+        exp = oracle.etag_multipart(md5s[pos:pos + c])
+        assert out[j].tobytes().hex() + f"-{c}" == exp
+        assert out[j].tobytes() == hashlib.md5(md5s[pos:pos + c].tobytes()).digest()
+        pos += c
+    # golden framing vector: parts {5 MiB 'a', 5 MiB 'b', 1 'c'}
+    fr = kat["framing"]
+    parts = [bytes([p["byte"]]) * p["count"] for p in fr["etag_parts"]]
+    d = eng.hash_batch(parts, MD5)[MD5]
+    assert eng.etag_combine(d, [3])[0].tobytes().hex() + "-3" == fr["etag"]
+
+
+def test_ring_many_slots_in_flight_and_wrap(torch):
+    from downloader_b200 import Engine
+    with Engine([0], ring_bytes=8 << 20) as e:
+        ln = 1 << 20
+        tickets = []
+        for k in range(20):  # 20 MiB through an 8 MiB ring: forces wrap + waits on the oldest slot
+            slot, view = e.ring_acquire(ln)
+            view[:] = oracle.synth(k, ln)
+            offs = np.arange(0, ln, 65536, dtype=np.uint64)
+            tickets.append((k, e.submit(slot, offs, np.full(offs.size, 65536, np.uint64), SHA1 | SHA256)))
+        for k, t in tickets:
+            r = e.result(t, 16, SHA1 | SHA256)
+            data = oracle.synth(k, ln)
+            bufs = [data[i * 65536:(i + 1) * 65536] for i in range(16)]
+            assert (r[SHA1] == ref_digests(SHA1, bufs)).all()
+            assert (r[SHA256] == ref_digests(SHA256, bufs)).all()
+        st = e.stats()
+        assert st["submits"] == 20 and st["launches"] == 40 and st["bytes"] == 20 * ln
+        assert st["h2d_bytes"] >= 20 * ln and st["kernel_ms"] > 0
+
+
+def test_completion_callback(eng):
+    import threading
+    ev = threading.Event()
+    seen = {}
+    slot, view = eng.ring_acquire(4096)
+    view[:] = 0
+    t = eng.submit(slot, [0], [4096], MD5, callback=lambda ticket, status: (seen.update(t=ticket, s=status), ev.set()))
+    assert ev.wait(30)
+    assert seen == {"t": t, "s": 0}
+    r = eng.result(t, 1, MD5)
+    assert r[MD5][0].tobytes() == hashlib.md5(bytes(4096)).digest()
+
+
+def test_errors_are_codes_not_crashes(eng):
+    from downloader_b200 import TritonHashError
+    slot, view = eng.ring_acquire(1024)
+    with pytest.raises(TritonHashError) as ei:
+        eng.submit(slot, [8], [16], SHA1)  # misaligned offset
+    assert ei.value.code == -5
+    with pytest.raises(TritonHashError) as ei:
+        eng.submit(slot, [0], [4096], SHA1)  # beyond the slot
+    assert ei.value.code == -1
+    eng.ring_release(slot)
+    with pytest.raises(TritonHashError) as ei:
+        eng.wait(123456789)
+    assert ei.value.code == -8
+    with pytest.raises(TritonHashError):
+        eng.ring_acquire(1 << 40)  # TH_ETOOBIG
+
+
+def test_config1_shape_one_gib_file_as_64_parts(torch, L, eng):
+    """BASELINE config 1 shape: 1 GiB file = 64 x 16 MiB parts, MD5 + SHA-256 + multipart ETag,
+    every part checked against libcrypto (the code path Node crypto runs)."""
+    n, ln = 64, 16 << 20
+    d = torch.empty(n * ln, dtype=torch.uint8, device="cuda")
+    L.th_synth_fill(d.data_ptr(), 0, n, ln, ln, oracle.DEFAULT_SEED, None)
+    offs = np.arange(n, dtype=np.uint64) * ln
+    t = eng.submit_device(d.data_ptr(), offs, np.full(n, ln, np.uint64), MD5 | SHA256)
+    r = eng.result(t, n, MD5 | SHA256)
+    host = d.cpu().numpy()
+    _, exp = oracle.evp_batch(MD5 | SHA256, host, offs, np.full(n, ln, np.uint64), threads=16, chunk=65536)
+    assert (r[MD5] == exp[MD5]).all() and (r[SHA256] == exp[SHA256]).all()
+    assert eng.etag_combine(r[MD5], [n])[0].tobytes().hex() + "-64" == oracle.etag_multipart(exp[MD5])
+
+
+def test_config2_full_size_properties(torch, L):
+    """BASELINE config 2 at full size: 65,536 x 256 KiB (16 GiB) SHA-1 + fused verify.
+    Size-independent checks: determinism across runs, bitfield flags exactly the corrupted pieces,
+    a stratified sample equals libcrypto."""
+    n, ln = 65536, 262144
+    free, _ = torch.cuda.mem_get_info()
+    if free < n * ln + (1 << 30):
+        pytest.skip("not enough free HBM")
+    d = torch.empty(n * ln, dtype=torch.uint8, device="cuda")
+    assert L.th_synth_fill(d.data_ptr(), 0, n, ln, ln, oracle.DEFAULT_SEED, None) == 0
+    out1 = torch.zeros(n * 20, dtype=torch.uint8, device="cuda")
+    out2 = torch.zeros(n * 20, dtype=torch.uint8, device="cuda")
+    ok = torch.zeros(n // 32, dtype=torch.int32, device="cuda")
+    assert L.th_sha1_batch(d.data_ptr(), None, None, None, ln, ln, n, out1.data_ptr(), None, None, None) == 0
+    exp = out1.clone()
+    bad = [0, 1, 4097, 32768, 65535]
+    for b in bad:
+        exp.view(n, 20)[b, 3] ^= 0x80
+    assert L.th_sha1_batch(d.data_ptr(), None, None, None, ln, ln, n, out2.data_ptr(), exp.data_ptr(), ok.data_ptr(), None) == 0
+    torch.cuda.synchronize()
+    assert torch.equal(out1, out2)
+    words = ok.cpu().numpy().view(np.uint32)
+    bits = ((words[np.arange(n) >> 5] >> (np.arange(n) & 31)) & 1).astype(bool)
+    assert sorted(np.nonzero(~bits)[0].tolist()) == bad
+    digs = out1.cpu().numpy().reshape(n, 20)
+    assert len({bytes(x) for x in digs[:: 64]}) == n // 64  # distinct messages -> distinct digests
+    pick = sorted(set(np.linspace(0, n - 1, 96).astype(int).tolist()))
+    host = np.concatenate([d[i * ln:(i + 1) * ln].cpu().numpy() for i in pick])
+    for j, i in enumerate(pick[:8]):  # the device bytes are the generator's bytes
+        assert (host[j * ln:(j + 1) * ln] == oracle.synth(i, ln)).all()
+    _, e = oracle.evp_batch(SHA1, host, (np.arange(len(pick)) * ln).astype(np.uint64), np.full(len(pick), ln, np.uint64), threads=16)
+    assert (digs[pick] == e[SHA1]).all()
