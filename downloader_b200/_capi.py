@@ -93,6 +93,8 @@ def lib() -> C.CDLL:
     L.th_synth_fill.argtypes = [vp, u64, u64, u64, u64, u64, vp]
     L.th_set_staging.argtypes = [u32, i32, i32]
     L.th_get_staging.argtypes = [u32, C.POINTER(i32), C.POINTER(i32)]
+    L.th_set_tiling.argtypes = [u32, i32, i32]
+    L.th_set_option.argtypes = [C.c_char_p, C.c_longlong]
     _lib = L
     return L
 

@@ -315,6 +315,102 @@ __device__ __forceinline__ void digest_stream(const uint8_t* __restrict__ msg, u
   }
 }
 
+// ------------------------------------------------------------------- 2-D tensor-map (TMA) staging
+// Equal-length messages a fixed stride apart form a 2-D byte tensor [n rows][len bytes].  One
+// cp.async.bulk.tensor.2d (SASS UTMALDG) then moves a {128 B x 32 rows} box — the next 128 bytes of
+// all 32 messages of a warp — into a 4 KiB shared-memory tile with the 128-byte swizzle, so lane r
+// reads its 16-byte piece q at tile + r*128 + ((q ^ (r & 7)) << 4): the eight lanes of every LDS.128
+// quarter-warp phase hit eight different bank groups.  Bytes past `len` and rows past n are
+// zero-filled by the TMA unit (no over-read); one elected lane issues, nobody loops.
+__device__ __forceinline__ void tma_tile_2d(uint32_t dst, const void* tmap, uint32_t c0, uint32_t c1, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
+      "l"(tmap), "r"(c0), "r"(c1), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ void prefetch_tmap(const void* tmap) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
+}
+
+template <int K, int NST>
+struct Tiles {
+  static_assert(K >= 1 && K <= 8 && NST >= 2 && NST <= 8, "bad tile geometry");
+  static constexpr int CH = 128 * K;            // message bytes per lane per stage
+  static constexpr int TILE = 4096;             // 32 rows x 128 B
+  static constexpr int STAGE_BYTES = K * TILE;
+  static constexpr int WARP_BYTES = NST * STAGE_BYTES;  // tiles only; mbarriers live elsewhere
+};
+
+// Per-warp pipeline state that survives across segments (stage cursor + one phase bit per stage).
+struct PipeState {
+  int stage = 0;
+  uint32_t phase = 0;
+};
+
+// Runs chunks [c_begin, c_end) of the warp's 32 equal-length messages (rows row0 .. row0+31 of the
+// tensor) through A::compress, continuing from chaining value h.  nch = len / CH + 1 is the chunk count
+// of a whole message; its last chunk is partial (possibly empty) and carries the padding block(s).
+// s_tiles: this warp's Tiles<K,NST>::WARP_BYTES (1024-byte aligned); s_bar: NST mbarriers (count 1).
+template <class A, int K, int NST>
+__device__ __forceinline__ void tile_segment(const void* tmap, uint32_t row0, uint64_t len, uint32_t c_begin,
+                                             uint32_t c_end, uint32_t nch, uint32_t* h, uint32_t s_tiles,
+                                             uint32_t s_bar, int lane, PipeState& ps) {
+  using G = Tiles<K, NST>;
+  constexpr int CH = G::CH;
+  auto issue = [&](uint32_t c, int s) {
+    if (lane == 0) {
+      const uint64_t pos = (uint64_t)c * CH;
+      const uint64_t left = pos < len ? len - pos : 0;
+      const uint32_t ntile = left >= (uint64_t)CH ? (uint32_t)K : (uint32_t)((left + 127) >> 7);
+      const uint32_t bar = s_bar + 8 * s;
+      mbar_arrive_expect_tx(bar, ntile * G::TILE);
+#pragma unroll
+      for (int j = 0; j < K; j++)
+        if ((uint32_t)j < ntile) tma_tile_2d(s_tiles + (s * K + j) * G::TILE, tmap, (uint32_t)pos + 128u * j, row0, bar);
+    }
+  };
+  {
+    int s = ps.stage;
+#pragma unroll
+    for (int i = 0; i < NST; i++) {
+      if (c_begin + i < c_end) issue(c_begin + i, s);
+      if (++s == NST) s = 0;
+    }
+  }
+  const uint32_t swz = (uint32_t)(lane & 7);
+  for (uint32_t c = c_begin; c < c_end; c++) {
+    const int s = ps.stage;
+    mbar_wait(s_bar + 8 * s, (ps.phase >> s) & 1u);
+    ps.phase ^= 1u << s;
+    const bool last = c == nch - 1u;
+    const uint32_t bytes = last ? (uint32_t)(len - (uint64_t)c * CH) : (uint32_t)CH;
+    const uint32_t nb = bytes >> 6, r = bytes & 63u;
+    const uint32_t nblk = nb + (last ? (r < 56 ? 1u : 2u) : 0u);
+    const uint32_t lane_base = s_tiles + s * G::STAGE_BYTES + lane * 128;
+    for (uint32_t b = 0; b < nblk; b++) {
+      uint32_t w[16];
+      const uint32_t bb = b < (uint32_t)(2 * K) ? b : 0u;  // padding block 1 past the stage: nothing to read
+      const uint32_t a = lane_base + (bb >> 1) * G::TILE;
+      const uint32_t q0 = (bb & 1u) * 4u;
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        uint4 v = lds128(a + (((q0 + q) ^ swz) << 4));
+        w[4 * q] = v.x; w[4 * q + 1] = v.y; w[4 * q + 2] = v.z; w[4 * q + 3] = v.w;
+      }
+      if (b >= nb) pad_block<A>(w, b - nb, r, len);
+      if (A::BE) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) w[i] = bswap(w[i]);
+      }
+      A::compress(h, w);
+    }
+    __syncwarp();
+    fence_proxy_async_smem();
+    if (c + NST < c_end) issue(c + NST, s);
+    if (++ps.stage == NST) ps.stage = 0;
+  }
+}
+
 // Writes the digest in its standard byte order (SHA: big-endian words; MD5: little-endian words).
 template <class A>
 __device__ __forceinline__ void store_digest(uint8_t* out, const uint32_t* h) {

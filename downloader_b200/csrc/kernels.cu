@@ -9,6 +9,8 @@
 //   synth_kernel             SURVEY §8d counter-based generator (benchmarks / tests).
 #include <cstdint>
 #include <cstdio>
+#include <string>
+#include <cuda.h>  // CUtensorMap types only; the encoder is fetched with cudaGetDriverEntryPoint (no -lcuda)
 #include <cuda_runtime.h>
 
 #include "../../include/tritonhash.h"
@@ -58,6 +60,126 @@ __global__ void __launch_bounds__(32) digest_kernel(const DigestArgs p) {
     } else {
       const uint32_t word = __ballot_sync(0xffffffffu, ok);
       if (lane == 0) p.ok_bits[blockIdx.x] = word;
+    }
+  }
+}
+
+// --------------------------------------------------------------- equal-length batches: tensor-map path
+struct TileArgs {
+  uint64_t len;
+  uint32_t n;
+  uint32_t segc;            // sliced kernel: chunks per segment
+  uint32_t nseg;            // sliced kernel: segments per message
+  uint8_t* out;
+  const uint8_t* expected;  // SHA-1 only, nullable
+  uint32_t* ok_bits;        // SHA-1 only, nullable
+};
+
+template <class A>
+__device__ __forceinline__ void finish_group(const TileArgs& p, uint32_t group, int lane, const uint32_t* h) {
+  const uint32_t idx = group * 32u + lane;
+  const bool valid = idx < p.n;
+  if (valid) store_digest<A>(p.out + (size_t)idx * A::DLEN, h);
+  if (A::DLEN == 20 && p.expected && p.ok_bits) {  // fused piece verification -> bitfield word
+    bool ok = false;
+    if (valid) {
+      const uint32_t* e = reinterpret_cast<const uint32_t*>(p.expected + (size_t)idx * 20);
+      ok = true;
+#pragma unroll
+      for (int i = 0; i < 5; i++) ok &= (__ldg(e + i) == bswap(h[i]));
+    }
+    const uint32_t word = __ballot_sync(0xffffffffu, ok);
+    if (lane == 0) p.ok_bits[group] = word;
+  }
+}
+
+// One warp = one CTA = 32 consecutive messages; used when messages are too few to fill the chip
+// (every group gets its own warp slot, and MD5 / SHA-256 kernels of one submit co-reside on an SM).
+template <class A, int K, int NST>
+__global__ void __launch_bounds__(32) digest_tile_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs p) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  using G = Tiles<K, NST>;
+  const int lane = threadIdx.x;
+  const uint32_t s_tiles = smem_u32(smem);
+  const uint32_t s_bar = s_tiles + G::WARP_BYTES;
+  if (lane == 0) {
+    prefetch_tmap(&tmap);
+#pragma unroll
+    for (int s = 0; s < NST; s++) mbar_init(s_bar + 8 * s, 1);
+    mbar_init_fence();
+  }
+  __syncwarp();
+  const uint32_t nch = (uint32_t)(p.len / G::CH) + 1u;
+  uint32_t h[A::NS];
+  A::init(h);
+  PipeState ps;
+  tile_segment<A, K, NST>(&tmap, blockIdx.x * 32u, p.len, 0u, nch, nch, h, s_tiles, s_bar, lane, ps);
+  finish_group<A>(p, blockIdx.x, lane, h);
+}
+
+// Persistent, time-sliced: one CTA per SM, W worker warps (a multiple of 4, so every SM sub-partition
+// holds the same number), G = this SM's share of the message groups.  A chain cannot be split across
+// threads, but it can be handed from warp to warp between blocks: its whole state is the chaining value.
+// So each group's message is cut into `nseg` segments and unit k = (segment k / G, group k % G) is run
+// by worker k % W.  With G > W the G chains advance round-robin at the same rate and all four
+// sub-partitions stay equally loaded until the end, instead of 4,4,3,3 warps finishing at different
+// times.  Chaining values travel through shared memory; done[g] counts finished segments.
+template <class A, int K, int NST>
+__global__ void __launch_bounds__(512, 1) digest_sliced_kernel(const __grid_constant__ CUtensorMap tmap,
+                                                               const TileArgs p) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  using G_ = Tiles<K, NST>;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t W = blockDim.x >> 5;
+  const uint32_t groups_total = (p.n + 31u) / 32u;
+  const uint32_t g0 = (uint32_t)(((uint64_t)blockIdx.x * groups_total) / gridDim.x);
+  const uint32_t g1 = (uint32_t)(((uint64_t)(blockIdx.x + 1) * groups_total) / gridDim.x);
+  const uint32_t G = g1 - g0;
+  const uint32_t s_tiles = smem_u32(smem) + warp * G_::WARP_BYTES;
+  const uint32_t s_bar = smem_u32(smem) + W * G_::WARP_BYTES + warp * (8 * NST);
+  // after the tiles and barriers: done[G] (u32, padded to 128 B), then state[G][NS][32]
+  unsigned char* tail = smem + W * G_::WARP_BYTES + ((W * 8 * NST + 127) & ~127u);
+  volatile uint32_t* done = reinterpret_cast<volatile uint32_t*>(tail);
+  uint32_t* state = reinterpret_cast<uint32_t*>(tail + ((G * 4 + 127) & ~127u));
+
+  if (lane == 0) {
+    if (warp == 0) prefetch_tmap(&tmap);
+#pragma unroll
+    for (int s = 0; s < NST; s++) mbar_init(s_bar + 8 * s, 1);
+    mbar_init_fence();
+  }
+  for (uint32_t g = threadIdx.x; g < G; g += blockDim.x) done[g] = 0;
+  __syncthreads();
+
+  const uint32_t nch = (uint32_t)(p.len / G_::CH) + 1u;
+  const uint32_t S = p.nseg;
+  PipeState ps;
+  const uint32_t units = G * S;
+  for (uint32_t k = warp; k < units; k += W) {
+    const uint32_t g = k % G, seg = k / G;
+    uint32_t h[A::NS];
+    if (seg == 0) {
+      A::init(h);
+    } else {
+      if (lane == 0) {
+        while (done[g] < seg) __nanosleep(64);
+      }
+      __syncwarp();
+      __threadfence_block();
+#pragma unroll
+      for (int i = 0; i < A::NS; i++) h[i] = state[(g * A::NS + i) * 32 + lane];
+    }
+    const uint32_t c_begin = seg * p.segc;
+    const uint32_t c_end = min(nch, c_begin + p.segc);
+    tile_segment<A, K, NST>(&tmap, (g0 + g) * 32u, p.len, c_begin, c_end, nch, h, s_tiles, s_bar, lane, ps);
+    if (seg == S - 1) {
+      finish_group<A>(p, g0 + g, lane, h);
+    } else {
+#pragma unroll
+      for (int i = 0; i < A::NS; i++) state[(g * A::NS + i) * 32 + lane] = h[i];
+      __threadfence_block();
+      __syncwarp();
+      if (lane == 0) done[g] = seg + 1;
     }
   }
 }
@@ -170,6 +292,128 @@ cudaError_t launch_variant(const DigestArgs& a, cudaStream_t st) {
   return cudaGetLastError();
 }
 
+// ---- tensor-map path (equal-length, fixed-stride batches) -------------------------------------------
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
+  return fn;
+}
+
+// Byte tensor [n rows][len bytes], row pitch `stride`; box {128 B, 32 rows}, 128-byte swizzle.
+static bool make_tmap(CUtensorMap* m, const void* base, uint64_t len, uint64_t stride, uint32_t n) {
+  EncodeTiledFn enc = encode_tiled();
+  if (!enc) return false;
+  const cuuint64_t gdim[2] = {len, n};
+  const cuuint64_t gstr[1] = {n > 1 ? stride : ((len + 15) & ~15ull)};
+  const cuuint32_t box[2] = {128, 32};
+  const cuuint32_t estr[2] = {1, 1};
+  return enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(base), gdim, gstr, box, estr,
+             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+struct TileOpts {
+  int path = 0;        // 0 auto, 1 per-lane bulk copies (any layout), 2 tile kernel, 3 sliced kernel
+  int workers = 12;    // sliced kernel: worker warps per SM (multiple of 4)
+  int rounds = 32;     // sliced kernel: target scheduling rounds (units per worker)
+  int sliced_min_groups = 592;  // auto: use the sliced kernel from this many 32-message groups
+};
+static TileOpts g_opts;
+
+using tile_fn = cudaError_t (*)(const CUtensorMap&, const TileArgs&, uint32_t grid, uint32_t block, size_t smem, cudaStream_t);
+
+template <class A, int K, int NST>
+cudaError_t launch_tile(const CUtensorMap& m, const TileArgs& a, uint32_t grid, uint32_t, size_t, cudaStream_t st) {
+  constexpr int smem = Tiles<K, NST>::WARP_BYTES + 8 * NST;
+  static bool set = false;
+  if (!set && smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(digest_tile_kernel<A, K, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    set = true;
+  }
+  digest_tile_kernel<A, K, NST><<<grid, 32, smem, st>>>(m, a);
+  return cudaGetLastError();
+}
+
+template <class A, int K, int NST>
+cudaError_t launch_sliced(const CUtensorMap& m, const TileArgs& a, uint32_t grid, uint32_t block, size_t smem, cudaStream_t st) {
+  static size_t set_to[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 64 && set_to[dev] < smem) {
+    cudaError_t e = cudaFuncSetAttribute(digest_sliced_kernel<A, K, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
+    set_to[dev] = 227 * 1024;
+  }
+  digest_sliced_kernel<A, K, NST><<<grid, block, smem, st>>>(m, a);
+  return cudaGetLastError();
+}
+
+struct TileVariant { int k, nst; tile_fn tile[3]; tile_fn sliced[3]; };
+#define TH_TILE_VARIANT(K, NST)                                                                         \
+  { K, NST, { launch_tile<Sha1, K, NST>, launch_tile<Md5, K, NST>, launch_tile<Sha256, K, NST> },          \
+    { launch_sliced<Sha1, K, NST>, launch_sliced<Md5, K, NST>, launch_sliced<Sha256, K, NST> } }
+static const TileVariant g_tile_variants[] = {
+    TH_TILE_VARIANT(1, 2), TH_TILE_VARIANT(1, 3), TH_TILE_VARIANT(1, 4),
+    TH_TILE_VARIANT(2, 2), TH_TILE_VARIANT(2, 3), TH_TILE_VARIANT(4, 2),
+};
+constexpr int kNumTileVariants = sizeof(g_tile_variants) / sizeof(g_tile_variants[0]);
+static int g_tile_selected[3] = {1, 1, 1};
+
+static size_t sliced_smem(int K, int NST, uint32_t W, uint32_t Gmax, int ns) {
+  return (size_t)W * K * NST * 4096 + ((W * 8 * NST + 127) & ~127u) + ((Gmax * 4 + 127) & ~127u) + (size_t)Gmax * ns * 128;
+}
+
+// Returns TH_OK if launched, 1 if this batch is not eligible (caller falls back to the bulk-copy kernel).
+static int launch_uniform(int ai, const void* d_base, uint64_t stride, uint64_t len, uint32_t n, uint8_t* d_out,
+                          const uint8_t* d_expected, uint32_t* d_ok_bits, cudaStream_t st) {
+  if (g_opts.path == 1) return 1;
+  if (len < 1024 || len >= (1ull << 31) || (n > 1 && (stride & 15)) || (n > 1 && stride < len) || stride >= (1ull << 40)) return 1;
+  CUtensorMap tmap;
+  if (!make_tmap(&tmap, d_base, len, stride, n)) return 1;
+  const TileVariant& v = g_tile_variants[g_tile_selected[ai]];
+  const int ns = ai == 0 ? 5 : ai == 1 ? 4 : 8;
+  TileArgs a{len, n, 0, 1, d_out, d_expected, d_ok_bits};
+  const uint32_t groups = (n + 31u) / 32u;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  bool sliced = g_opts.path == 3 || (g_opts.path == 0 && groups >= (uint32_t)g_opts.sliced_min_groups);
+  if (sliced) {
+    const uint32_t W = (uint32_t)g_opts.workers;
+    const uint32_t grid = groups < (uint32_t)sms ? groups : (uint32_t)sms;
+    const uint32_t Gmax = (groups + grid - 1) / grid;
+    const uint32_t nch = (uint32_t)(len / (128u * v.k)) + 1u;
+    uint32_t S = 1;
+    if (Gmax > W && Gmax < 4 * W) {  // few chains per worker: cut them so that ~rounds units run per worker
+      S = ((uint32_t)g_opts.rounds * W + Gmax - 1) / Gmax;
+      const uint32_t smax = nch / 4 ? nch / 4 : 1;  // at least 4 chunks per segment
+      if (S > smax) S = smax;
+      if (S < 1) S = 1;
+    }
+    a.segc = (nch + S - 1) / S;
+    a.nseg = (nch + a.segc - 1) / a.segc;
+    const size_t smem = sliced_smem(v.k, v.nst, W, Gmax, ns);
+    if (smem <= 227 * 1024) {
+      cudaError_t e = v.sliced[ai](tmap, a, grid, W * 32, smem, st);
+      return e == cudaSuccess ? TH_OK : TH_ECUDA;
+    }
+    // state does not fit: fall through to the one-warp-per-CTA kernel
+  }
+  cudaError_t e = v.tile[ai](tmap, a, groups, 32, 0, st);
+  return e == cudaSuccess ? TH_OK : TH_ECUDA;
+}
+
 struct Variant { int ch, nst; launch_fn fn[3]; };
 #define TH_VARIANT(CH, NST) \
   { CH, NST, { launch_variant<Sha1, CH, NST>, launch_variant<Md5, CH, NST>, launch_variant<Sha256, CH, NST> } }
@@ -194,6 +438,10 @@ static int launch_digest(uint32_t alg, const void* d_base, const uint64_t* d_off
   if ((reinterpret_cast<uintptr_t>(d_base) & 15) != 0) return TH_EALIGN;
   if (!d_offsets && (stride & 15) != 0 && n > 1) return TH_EALIGN;
   if (!d_lengths && len >= (1ull << 37)) return TH_ETOOBIG;
+  if (!d_offsets && !d_lengths && !d_order) {  // equal-length, fixed-stride batch -> tensor-map kernels
+    const int rc = launch_uniform(ai, d_base, stride, len, n, d_out, d_expected, d_ok_bits, static_cast<cudaStream_t>(stream));
+    if (rc <= 0) return rc;
+  }
   DigestArgs a{static_cast<const uint8_t*>(d_base), d_offsets, d_lengths, d_order, stride, len, n, d_out,
                d_expected, d_ok_bits};
   cudaError_t e = g_variants[g_selected[ai]].fn[ai](a, static_cast<cudaStream_t>(stream));
@@ -255,6 +503,28 @@ int th_set_staging(uint32_t alg, int chunk_bytes, int stages) {
     if (th::g_variants[v].ch == chunk_bytes && th::g_variants[v].nst == stages) {
       for (int a = 0; a < 3; a++)
         if (alg & (1u << a)) { th::g_selected[a] = v; rc = TH_OK; }
+    }
+  }
+  return rc;
+}
+
+int th_set_option(const char* name, long long value) {
+  if (!name) return TH_EINVAL;
+  const std::string k(name);
+  if (k == "path") { if (value < 0 || value > 3) return TH_EINVAL; th::g_opts.path = (int)value; return TH_OK; }
+  if (k == "workers") { if (value < 4 || value > 16 || value % 4) return TH_EINVAL; th::g_opts.workers = (int)value; return TH_OK; }
+  if (k == "rounds") { if (value < 1 || value > 4096) return TH_EINVAL; th::g_opts.rounds = (int)value; return TH_OK; }
+  if (k == "sliced_min_groups") { if (value < 1) return TH_EINVAL; th::g_opts.sliced_min_groups = (int)value; return TH_OK; }
+  if (k == "tile_k" || k == "tile_stages") return TH_EINVAL;  // use th_set_tiling
+  return TH_EINVAL;
+}
+
+int th_set_tiling(uint32_t alg, int tiles_per_stage, int stages) {
+  int rc = TH_EINVAL;
+  for (int v = 0; v < th::kNumTileVariants; v++) {
+    if (th::g_tile_variants[v].k == tiles_per_stage && th::g_tile_variants[v].nst == stages) {
+      for (int a = 0; a < 3; a++)
+        if (alg & (1u << a)) { th::g_tile_selected[a] = v; rc = TH_OK; }
     }
   }
   return rc;

@@ -153,6 +153,14 @@ int th_synth_fill(void* d_dst, uint64_t first_msg, uint64_t n, uint64_t len, uin
  * variant was compiled.  Defaults are the tuned values in DESIGN.md. */
 int th_set_staging(uint32_t alg, int chunk_bytes, int stages);
 int th_get_staging(uint32_t alg, int* chunk_bytes, int* stages);
+/* Equal-length, fixed-stride batches (all pieces of a torrent but the last, all parts of an object
+ * but the last) take the tensor-map kernels: a {128 B x 32 messages} TMA box per copy.  This picks how
+ * many such tiles a warp stages per pipeline stage (1, 2, 4) and the number of stages (2..4). */
+int th_set_tiling(uint32_t alg, int tiles_per_stage, int stages);
+/* Tuning knobs (process-wide): "path" 0 auto | 1 per-lane bulk copies | 2 one-warp CTAs on tensor-map
+ * tiles | 3 persistent time-sliced kernel; "workers" 4|8|12|16 warps per SM for path 3; "rounds"
+ * scheduling rounds per worker for path 3; "sliced_min_groups" auto threshold (32-message groups). */
+int th_set_option(const char* name, long long value);
 
 #ifdef __cplusplus
 }

@@ -123,6 +123,75 @@ def test_launch_level_uniform_batches(torch, L, n, ln):
         assert (oracle.batch(a, host, off, lens, threads=8) == exp[a]).all()
 
 
+TILINGS = [(1, 2), (1, 3), (1, 4), (2, 2), (2, 3), (4, 2)]
+
+
+@pytest.mark.parametrize("path", [1, 2, 3])
+@pytest.mark.parametrize("k,nst", TILINGS)
+def test_uniform_batch_paths_and_tilings(torch, L, path, k, nst):
+    """Equal-length batches: per-lane bulk copies (1), tensor-map tiles with one-warp CTAs (2) and the
+    persistent time-sliced kernel (3) must all give the oracle's digests, for every tiling, including
+    lengths that end mid-tile / mid-block and group counts that do not divide by the worker count."""
+    try:
+        assert L.th_set_option(b"path", path) == 0
+        assert L.th_set_tiling(7, k, nst) == 0
+        cases = [(70, 1024), (33, 128 * k * nst + 57), (1500, 4096 + 119), (2100, 2048 + 64), (64, 65536 + 56)]
+        if path == 3:
+            assert L.th_set_option(b"workers", 8 if k * nst > 4 else 12) == 0
+        for n, ln in cases:
+            stride = (ln + 15) & ~15
+            d = torch.zeros(n * stride, dtype=torch.uint8, device="cuda")
+            assert L.th_synth_fill(d.data_ptr(), 0, n, ln, stride, 99, None) == 0
+            outs = {a: torch.zeros(n * oracle.DIGEST_LEN[a], dtype=torch.uint8, device="cuda") for a in (SHA1, MD5, SHA256)}
+            assert L.th_sha1_batch(d.data_ptr(), None, None, None, stride, ln, n, outs[SHA1].data_ptr(), None, None, None) == 0
+            assert L.th_md5_batch(d.data_ptr(), None, None, None, stride, ln, n, outs[MD5].data_ptr(), None) == 0
+            assert L.th_sha256_batch(d.data_ptr(), None, None, None, stride, ln, n, outs[SHA256].data_ptr(), None) == 0
+            torch.cuda.synchronize()
+            host = d.cpu().numpy()
+            off = (np.arange(n) * stride).astype(np.uint64)
+            lens = np.full(n, ln, np.uint64)
+            for a in (SHA1, MD5, SHA256):
+                exp = oracle.batch(a, host, off, lens, threads=8)
+                got = outs[a].cpu().numpy().reshape(n, -1)
+                bad = np.nonzero((got != exp).any(axis=1))[0]
+                assert bad.size == 0, (NAMES[a], path, k, nst, n, ln, bad[:8])
+    finally:
+        L.th_set_option(b"path", 0)
+        L.th_set_option(b"workers", 12)
+        L.th_set_tiling(7, 1, 3)
+
+
+def test_sliced_kernel_time_slicing_engaged(torch, L):
+    """Config-2-like shape scaled down: ~14 groups per SM on 12 workers -> chains are cut into segments
+    and handed between warps; result must not change."""
+    n, ln = 148 * 14 * 32 - 40, 8192 + 64
+    d = torch.empty(n * ln, dtype=torch.uint8, device="cuda")
+    L.th_synth_fill(d.data_ptr(), 0, n, ln, ln, 5, None)
+    try:
+        res = {}
+        for path in (2, 3):
+            assert L.th_set_option(b"path", path) == 0
+            o = torch.zeros(n * 20, dtype=torch.uint8, device="cuda")
+            ok = torch.full(((n + 31) // 32,), -1, dtype=torch.int32, device="cuda")
+            assert L.th_sha1_batch(d.data_ptr(), None, None, None, ln, ln, n, o.data_ptr(), None, None, None) == 0
+            exp = o.clone()
+            exp.view(n, 20)[n - 1, 0] ^= 1
+            exp.view(n, 20)[12345, 19] ^= 1
+            assert L.th_sha1_batch(d.data_ptr(), None, None, None, ln, ln, n, o.data_ptr(), exp.data_ptr(), ok.data_ptr(), None) == 0
+            torch.cuda.synchronize()
+            res[path] = (o.cpu().numpy(), ok.cpu().numpy().view(np.uint32))
+        assert (res[2][0] == res[3][0]).all() and (res[2][1] == res[3][1]).all()
+        words = res[3][1]
+        bits = ((words[np.arange(n) >> 5] >> (np.arange(n) & 31)) & 1).astype(bool)
+        assert sorted(np.nonzero(~bits)[0].tolist()) == [12345, n - 1]
+        pick = [0, 1, 31, 32, 5000, n - 1]
+        host = np.concatenate([oracle.synth(i, ln, seed=5) for i in pick])
+        e = oracle.batch(SHA1, host, (np.arange(len(pick)) * ln).astype(np.uint64), np.full(len(pick), ln, np.uint64))
+        assert (res[3][0].reshape(n, 20)[pick] == e).all()
+    finally:
+        L.th_set_option(b"path", 0)
+
+
 def test_fused_verify_bitfield_identity_order(torch, L):
     """webtorrent's `hash === _hashes[i]` -> bitfield, fused into the SHA-1 kernel (uniform batch)."""
     n, ln = 2000, 16384

@@ -24,19 +24,29 @@ def main():
     ap.add_argument("--algs", default="sha1,md5,sha256")
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--variants", default="")
+    ap.add_argument("--path", type=int, default=1, help="1 bulk (variants = CHxNST), 2 tile, 3 sliced (variants = KxNST)")
+    ap.add_argument("--workers", default="12")
+    ap.add_argument("--rounds", default="32")
     a = ap.parse_args()
     L = _capi.lib()
     n, ln = a.n, a.len
     data = torch.empty(n * ln, dtype=torch.uint8, device="cuda")
     L.th_synth_fill(data.data_ptr(), 0, n, ln, ln, 1, None)
-    variants = VARIANTS if not a.variants else [tuple(map(int, v.split("x"))) for v in a.variants.split(",")]
+    TILINGS = [(1, 2), (1, 3), (1, 4), (2, 2), (2, 3), (4, 2)]
+    variants = (VARIANTS if a.path == 1 else TILINGS) if not a.variants else [tuple(map(int, v.split("x"))) for v in a.variants.split(",")]
+    assert L.th_set_option(b"path", a.path) == 0
+    combos = [(int(w), int(r)) for w in a.workers.split(",") for r in a.rounds.split(",")] if a.path == 3 else [(12, 32)]
     for alg in a.algs.split(","):
         out = torch.zeros(n * DL[alg], dtype=torch.uint8, device="cuda")
         fn = {"sha1": lambda: L.th_sha1_batch(data.data_ptr(), None, None, None, ln, ln, n, out.data_ptr(), None, None, None),
               "md5": lambda: L.th_md5_batch(data.data_ptr(), None, None, None, ln, ln, n, out.data_ptr(), None),
               "sha256": lambda: L.th_sha256_batch(data.data_ptr(), None, None, None, ln, ln, n, out.data_ptr(), None)}[alg]
-        for ch, st in variants:
-            assert L.th_set_staging(ALG[alg], ch, st) == 0
+        for (ch, st), (wk, rd) in [(v, c) for v in variants for c in combos]:
+            if a.path == 1:
+                assert L.th_set_staging(ALG[alg], ch, st) == 0
+            else:
+                assert L.th_set_tiling(ALG[alg], ch, st) == 0
+                assert L.th_set_option(b"workers", wk) == 0 and L.th_set_option(b"rounds", rd) == 0
             for _ in range(2):
                 assert fn() == 0
             torch.cuda.synchronize()
@@ -47,7 +57,7 @@ def main():
             e1.record()
             torch.cuda.synchronize()
             ms = e0.elapsed_time(e1) / a.iters
-            print(json.dumps({"alg": alg, "n": n, "len": ln, "chunk": ch, "stages": st, "ms": round(ms, 3),
+            print(json.dumps({"alg": alg, "path": a.path, "n": n, "len": ln, "chunk_or_k": ch, "stages": st, "workers": wk, "rounds": rd, "ms": round(ms, 3),
                               "GBps": round(n * ln / ms / 1e6, 1)}), flush=True)
 
 
