@@ -184,7 +184,8 @@ def main():
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--e2e-slots", type=int, default=8)
-    ap.add_argument("--staging", default="", help="override staging geometry, e.g. 512x2 (tuning only)")
+    ap.add_argument("--staging", default="", help="override bulk staging geometry, e.g. 512x2 (tuning only)")
+    ap.add_argument("--path", type=int, default=0, help="0 auto, 1 bulk, 2 tile, 3 sliced (tuning only)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":
@@ -200,6 +201,7 @@ def main():
     if args.staging:
         ch_, st_ = map(int, args.staging.split("x"))
         assert L.th_set_staging(7, ch_, st_) == 0, "no such staging variant"
+    assert L.th_set_option(b"path", args.path) == 0
     algs, n, ln, desc = WORKLOADS[args.workload]
     if args.messages:
         n = args.messages
@@ -383,7 +385,7 @@ def main():
         "vs_baseline": None, "dtype": "u32", "data": "synthetic",
         "config": {"workload": desc, "algs": algs, "messages_per_gpu": n, "message_bytes": ln,
                    "l2": "inputs (%.1f GiB per GPU) exceed the 126 MB L2; no flush" % (total_bytes / 2**30),
-                   "staging": dict(zip(("chunk_bytes", "stages"), _staging(L, algs))),
+                   "kernel": _plan(algs, ln, n),
                    "verified_vs_oracle": checked, "fused_compare": algs == "sha1"},
         "roofline": roofline, "clocks": clocks, "gpu_launches": launches_per_step * args.steps,
     }
@@ -406,10 +408,11 @@ def main():
     return 0
 
 
-def _staging(L, algs):
-    ch, st = C.c_int(), C.c_int()
-    L.th_get_staging({"sha1": 1, "md5+sha256": 4}[algs], C.byref(ch), C.byref(st))
-    return ch.value, st.value
+def _plan(algs, ln, n):
+    from downloader_b200 import _capi
+    if algs == "sha1":
+        return _capi.plan(1, ln, ln, n)
+    return {"md5": _capi.plan(2, ln, ln, n), "sha256": _capi.plan(4, ln, ln, n)}
 
 
 if __name__ == "__main__":

@@ -95,6 +95,7 @@ def lib() -> C.CDLL:
     L.th_get_staging.argtypes = [u32, C.POINTER(i32), C.POINTER(i32)]
     L.th_set_tiling.argtypes = [u32, i32, i32]
     L.th_set_option.argtypes = [C.c_char_p, C.c_longlong]
+    L.th_plan.argtypes = [u32, u64, u64, u32, C.c_char_p, C.c_size_t]
     _lib = L
     return L
 
@@ -105,6 +106,12 @@ def check(code: int, where: str, ctx=None) -> None:
         if ctx is not None and code == -3:
             detail = lib().th_last_error(ctx).decode()
         raise TritonHashError(code, where, detail)
+
+
+def plan(alg: int, length: int, stride: int, n: int) -> str:
+    buf = C.create_string_buffer(512)
+    check(lib().th_plan(alg, length, stride, n, buf, 512), "th_plan")
+    return buf.value.decode()
 
 
 def hex_(b: bytes) -> str:

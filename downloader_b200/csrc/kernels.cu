@@ -368,28 +368,34 @@ static const TileVariant g_tile_variants[] = {
     TH_TILE_VARIANT(2, 2), TH_TILE_VARIANT(2, 3), TH_TILE_VARIANT(4, 2),
 };
 constexpr int kNumTileVariants = sizeof(g_tile_variants) / sizeof(g_tile_variants[0]);
-static int g_tile_selected[3] = {1, 1, 1};
+static int g_tile_selected[3] = {5, 5, 5};    // one-warp CTAs: 4 tiles x 2 stages
+static int g_sliced_selected[3] = {3, 3, 3};  // persistent kernel: 2 tiles x 2 stages
 
 static size_t sliced_smem(int K, int NST, uint32_t W, uint32_t Gmax, int ns) {
   return (size_t)W * K * NST * 4096 + ((W * 8 * NST + 127) & ~127u) + ((Gmax * 4 + 127) & ~127u) + (size_t)Gmax * ns * 128;
 }
 
-// Returns TH_OK if launched, 1 if this batch is not eligible (caller falls back to the bulk-copy kernel).
-static int launch_uniform(int ai, const void* d_base, uint64_t stride, uint64_t len, uint32_t n, uint8_t* d_out,
-                          const uint8_t* d_expected, uint32_t* d_ok_bits, cudaStream_t st) {
-  if (g_opts.path == 1) return 1;
-  if (len < 1024 || len >= (1ull << 31) || (n > 1 && (stride & 15)) || (n > 1 && stride < len) || stride >= (1ull << 40)) return 1;
-  CUtensorMap tmap;
-  if (!make_tmap(&tmap, d_base, len, stride, n)) return 1;
-  const TileVariant& v = g_tile_variants[g_tile_selected[ai]];
+struct Plan {
+  int path = 1;  // 1 bulk, 2 tile, 3 sliced
+  int k = 0, nst = 0;
+  uint32_t grid = 0, block = 32, workers = 0, segc = 0, nseg = 1, groups_per_cta = 0;
+  size_t smem = 0;
+};
+
+// Chooses the kernel for an equal-length, fixed-stride batch (path 1 = not eligible for tensor maps).
+static Plan make_plan(int ai, uint64_t stride, uint64_t len, uint32_t n) {
+  Plan pl;
+  if (g_opts.path == 1) return pl;
+  if (len < 1024 || len >= (1ull << 31) || (n > 1 && (stride & 15)) || (n > 1 && stride < len) || stride >= (1ull << 40)) return pl;
+  if (!encode_tiled()) return pl;
   const int ns = ai == 0 ? 5 : ai == 1 ? 4 : 8;
-  TileArgs a{len, n, 0, 1, d_out, d_expected, d_ok_bits};
   const uint32_t groups = (n + 31u) / 32u;
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  bool sliced = g_opts.path == 3 || (g_opts.path == 0 && groups >= (uint32_t)g_opts.sliced_min_groups);
+  const bool sliced = g_opts.path == 3 || (g_opts.path == 0 && groups >= (uint32_t)g_opts.sliced_min_groups);
   if (sliced) {
+    const TileVariant& v = g_tile_variants[g_sliced_selected[ai]];
     const uint32_t W = (uint32_t)g_opts.workers;
     const uint32_t grid = groups < (uint32_t)sms ? groups : (uint32_t)sms;
     const uint32_t Gmax = (groups + grid - 1) / grid;
@@ -401,16 +407,31 @@ static int launch_uniform(int ai, const void* d_base, uint64_t stride, uint64_t 
       if (S > smax) S = smax;
       if (S < 1) S = 1;
     }
-    a.segc = (nch + S - 1) / S;
-    a.nseg = (nch + a.segc - 1) / a.segc;
     const size_t smem = sliced_smem(v.k, v.nst, W, Gmax, ns);
     if (smem <= 227 * 1024) {
-      cudaError_t e = v.sliced[ai](tmap, a, grid, W * 32, smem, st);
-      return e == cudaSuccess ? TH_OK : TH_ECUDA;
+      pl.path = 3; pl.k = v.k; pl.nst = v.nst; pl.grid = grid; pl.block = W * 32; pl.workers = W;
+      pl.segc = (nch + S - 1) / S; pl.nseg = (nch + pl.segc - 1) / pl.segc; pl.groups_per_cta = Gmax; pl.smem = smem;
+      return pl;
     }
-    // state does not fit: fall through to the one-warp-per-CTA kernel
+    // chaining-value slots do not fit beside the tiles: use the one-warp-per-CTA kernel
   }
-  cudaError_t e = v.tile[ai](tmap, a, groups, 32, 0, st);
+  const TileVariant& v = g_tile_variants[g_tile_selected[ai]];
+  pl.path = 2; pl.k = v.k; pl.nst = v.nst; pl.grid = groups; pl.block = 32;
+  pl.smem = (size_t)v.k * v.nst * 4096 + 8 * v.nst;
+  return pl;
+}
+
+// Returns TH_OK if launched, 1 if this batch is not eligible (caller falls back to the bulk-copy kernel).
+static int launch_uniform(int ai, const void* d_base, uint64_t stride, uint64_t len, uint32_t n, uint8_t* d_out,
+                          const uint8_t* d_expected, uint32_t* d_ok_bits, cudaStream_t st) {
+  const Plan pl = make_plan(ai, stride, len, n);
+  if (pl.path == 1) return 1;
+  CUtensorMap tmap;
+  if (!make_tmap(&tmap, d_base, len, stride, n)) return 1;
+  TileArgs a{len, n, pl.segc, pl.nseg, d_out, d_expected, d_ok_bits};
+  const TileVariant& v = g_tile_variants[pl.path == 3 ? g_sliced_selected[ai] : g_tile_selected[ai]];
+  cudaError_t e = pl.path == 3 ? v.sliced[ai](tmap, a, pl.grid, pl.block, pl.smem, st)
+                               : v.tile[ai](tmap, a, pl.grid, 32, 0, st);
   return e == cudaSuccess ? TH_OK : TH_ECUDA;
 }
 
@@ -422,7 +443,7 @@ static const Variant g_variants[] = {
     TH_VARIANT(256, 2), TH_VARIANT(256, 3), TH_VARIANT(512, 2),
 };
 constexpr int kNumVariants = sizeof(g_variants) / sizeof(g_variants[0]);
-static int g_selected[3] = {2, 2, 2};  // index into g_variants per algorithm: sha1, md5, sha256
+static int g_selected[3] = {6, 2, 6};  // index into g_variants per algorithm: sha1, md5, sha256
 
 static int alg_index(uint32_t alg) {
   return alg == TH_ALG_SHA1 ? 0 : alg == TH_ALG_MD5 ? 1 : alg == TH_ALG_SHA256 ? 2 : -1;
@@ -524,10 +545,29 @@ int th_set_tiling(uint32_t alg, int tiles_per_stage, int stages) {
   for (int v = 0; v < th::kNumTileVariants; v++) {
     if (th::g_tile_variants[v].k == tiles_per_stage && th::g_tile_variants[v].nst == stages) {
       for (int a = 0; a < 3; a++)
-        if (alg & (1u << a)) { th::g_tile_selected[a] = v; rc = TH_OK; }
+        if (alg & (1u << a)) { th::g_tile_selected[a] = v; th::g_sliced_selected[a] = v; rc = TH_OK; }
     }
   }
   return rc;
+}
+
+int th_plan(uint32_t alg, uint64_t len, uint64_t stride, uint32_t n, char* out, size_t cap) {
+  const int ai = th::alg_index(alg);
+  if (ai < 0 || !out || cap == 0) return TH_EINVAL;
+  const th::Plan pl = th::make_plan(ai, stride, len, n);
+  if (pl.path == 1) {
+    const th::Variant& v = th::g_variants[th::g_selected[ai]];
+    snprintf(out, cap, "bulk: one-warp CTAs, per-lane cp.async.bulk, %d B x %d stages, grid %u", v.ch, v.nst, (n + 31u) / 32u);
+  } else if (pl.path == 2) {
+    snprintf(out, cap, "tile: one-warp CTAs, TMA 2-D {128B x 32 msgs} x %d tiles x %d stages, grid %u, smem %zu B", pl.k,
+             pl.nst, pl.grid, pl.smem);
+  } else {
+    snprintf(out, cap,
+             "sliced: persistent %u CTAs x %u warps, TMA 2-D {128B x 32 msgs} x %d tiles x %d stages, <=%u groups/CTA, "
+             "%u segments of %u chunks, smem %zu B",
+             pl.grid, pl.workers, pl.k, pl.nst, pl.groups_per_cta, pl.nseg, pl.segc, pl.smem);
+  }
+  return TH_OK;
 }
 
 int th_get_staging(uint32_t alg, int* chunk_bytes, int* stages) {

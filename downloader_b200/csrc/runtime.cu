@@ -168,19 +168,30 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, size_t copy_off
   uint64_t* h_len = reinterpret_cast<uint64_t*>(jb->h + jb->o_len(n));
   uint32_t* h_ord = reinterpret_cast<uint32_t*>(jb->h + jb->o_ord(n));
   uint64_t total = 0;
-  bool uniform = true;
   for (size_t i = 0; i < n; i++) {
     h_off[i] = msgs[i].offset;
     h_len[i] = msgs[i].length;
     total += msgs[i].length;
-    uniform &= (msgs[i].length / 64 == msgs[0].length / 64);
   }
-  // Length bucketing: a warp runs as long as its longest message, so lanes are dealt messages in
-  // descending block-count order (stable).  Equal-length batches keep the identity mapping.
-  const bool use_order = !uniform;
+  // Equal-length prefix at a fixed stride (all pieces of a torrent / parts of an object but the last):
+  // goes to the tensor-map kernels.  m is kept a multiple of 32 so the verify bitfield splits on a word.
+  size_t m = 0;
+  uint64_t ulen = msgs[0].length, ustride = n > 1 ? msgs[1].offset - msgs[0].offset : ((msgs[0].length + 15) & ~15ull);
+  if (ulen >= 1024 && ulen < (1ull << 31) && (ustride & 15) == 0 && ustride >= ulen && (n == 1 || msgs[1].offset > msgs[0].offset)) {
+    m = 1;
+    while (m < n && msgs[m].length == ulen && msgs[m].offset == msgs[0].offset + m * ustride) m++;
+    if (m < n) m &= ~(size_t)31;
+    if (m < 64 && m < n) m = 0;
+  }
+  const size_t rest = n - m;
+  // Length bucketing for the remainder: a warp runs as long as its longest message, so lanes are dealt
+  // messages in descending block-count order (stable).  Equal-length remainders keep the identity mapping.
+  bool rest_uniform = true;
+  for (size_t i = m; i < n; i++) rest_uniform &= (h_len[i] / 64 == h_len[m] / 64);
+  const bool use_order = rest > 0 && !rest_uniform;
   if (use_order) {
-    std::iota(h_ord, h_ord + n, 0u);
-    std::stable_sort(h_ord, h_ord + n, [&](uint32_t a, uint32_t b) { return h_len[a] / 64 > h_len[b] / 64; });
+    std::iota(h_ord + m, h_ord + n, 0u);  // indices relative to the remainder
+    std::stable_sort(h_ord + m, h_ord + n, [&](uint32_t a, uint32_t b) { return h_len[m + a] / 64 > h_len[m + b] / 64; });
   }
   if (expected) std::memcpy(jb->h + jb->o_exp(n), expected, n * 20);
 
@@ -197,12 +208,14 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, size_t copy_off
   CU(c, cudaEventCreateWithFlags(&ev_in, cudaEventDisableTiming));
   CU(c, cudaEventRecord(ev_in, g.s_copy));
 
-  const uint64_t* d_off = reinterpret_cast<const uint64_t*>(jb->d + jb->o_off(n));
-  const uint64_t* d_len = reinterpret_cast<const uint64_t*>(jb->d + jb->o_len(n));
-  const uint32_t* d_ord = use_order ? reinterpret_cast<const uint32_t*>(jb->d + jb->o_ord(n)) : nullptr;
+  const uint64_t* d_off = reinterpret_cast<const uint64_t*>(jb->d + jb->o_off(n)) + m;
+  const uint64_t* d_len = reinterpret_cast<const uint64_t*>(jb->d + jb->o_len(n)) + m;
+  const uint32_t* d_ord = use_order ? reinterpret_cast<const uint32_t*>(jb->d + jb->o_ord(n)) + m : nullptr;
   const size_t out_off[3] = {jb->o_sha1(n), jb->o_md5(n), jb->o_sha256(n)};
   const size_t out_len[3] = {n * 20, n * 16, n * 32};
+  const size_t dlen[3] = {20, 16, 32};
   const size_t ok_bytes = ((n + 31) / 32) * 4;
+  const uint8_t* d_uni = d_base + msgs[0].offset;
 
   for (int a = 0; a < 3; a++) {
     if (!(mask & (1u << a))) continue;
@@ -211,25 +224,35 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, size_t copy_off
     int rc = TH_OK;
     CU(c, cudaEventCreate(&t->ev_k0[a]));
     CU(c, cudaEventCreate(&t->ev_k1[a]));
-    if (a == 0) {
-      uint32_t* d_ok = expected ? reinterpret_cast<uint32_t*>(jb->d + jb->o_ok(n)) : nullptr;
-      if (d_ok && use_order) CU(c, cudaMemsetAsync(d_ok, 0, ok_bytes, st));
-      CU(c, cudaEventRecord(t->ev_k0[a], st));
-      rc = th_sha1_batch(d_base, d_off, d_len, d_ord, 0, 0, (uint32_t)n, jb->d + out_off[0],
-                         expected ? jb->d + jb->o_exp(n) : nullptr, d_ok, st);
-    } else if (a == 1) {
-      CU(c, cudaEventRecord(t->ev_k0[a], st));
-      rc = th_md5_batch(d_base, d_off, d_len, d_ord, 0, 0, (uint32_t)n, jb->d + out_off[1], st);
-    } else {
-      CU(c, cudaEventRecord(t->ev_k0[a], st));
-      rc = th_sha256_batch(d_base, d_off, d_len, d_ord, 0, 0, (uint32_t)n, jb->d + out_off[2], st);
+    uint8_t* d_out = jb->d + out_off[a];
+    const uint8_t* d_exp = (a == 0 && expected) ? jb->d + jb->o_exp(n) : nullptr;
+    uint32_t* d_ok = (a == 0 && expected) ? reinterpret_cast<uint32_t*>(jb->d + jb->o_ok(n)) : nullptr;
+    if (d_ok && use_order) CU(c, cudaMemsetAsync(d_ok + m / 32, 0, ok_bytes - (m / 32) * 4, st));
+    CU(c, cudaEventRecord(t->ev_k0[a], st));
+    for (int part = 0; part < 2 && rc == TH_OK; part++) {
+      const bool uni = part == 0;
+      const size_t cnt = uni ? m : rest;
+      if (cnt == 0) continue;
+      const size_t first = uni ? 0 : m;
+      const uint8_t* pb = uni ? d_uni : d_base;
+      const uint64_t* po = uni ? nullptr : d_off;
+      const uint64_t* pl = uni ? nullptr : d_len;
+      const uint32_t* pr = uni ? nullptr : d_ord;
+      uint8_t* o = d_out + first * dlen[a];
+      if (a == 0)
+        rc = th_sha1_batch(pb, po, pl, pr, ustride, ulen, (uint32_t)cnt, o, d_exp ? d_exp + first * 20 : nullptr,
+                           d_ok ? d_ok + first / 32 : nullptr, st);
+      else if (a == 1)
+        rc = th_md5_batch(pb, po, pl, pr, ustride, ulen, (uint32_t)cnt, o, st);
+      else
+        rc = th_sha256_batch(pb, po, pl, pr, ustride, ulen, (uint32_t)cnt, o, st);
+      g.st.launches += 1;
     }
     if (rc != TH_OK) {
       if (rc == TH_ECUDA) return cuda_fail(c, cudaGetLastError(), "digest kernel launch");
       return rc;
     }
     CU(c, cudaEventRecord(t->ev_k1[a], st));
-    g.st.launches += 1;
     g.st.messages += n;
     CU(c, cudaMemcpyAsync(jb->h + out_off[a], jb->d + out_off[a], out_len[a], cudaMemcpyDeviceToHost, st));
     g.st.d2h_bytes += out_len[a];

@@ -161,6 +161,9 @@ int th_set_tiling(uint32_t alg, int tiles_per_stage, int stages);
  * tiles | 3 persistent time-sliced kernel; "workers" 4|8|12|16 warps per SM for path 3; "rounds"
  * scheduling rounds per worker for path 3; "sliced_min_groups" auto threshold (32-message groups). */
 int th_set_option(const char* name, long long value);
+/* Describes, as text, the kernel and geometry an equal-length batch of n messages would be run
+ * with on the current device (what benchmarks record next to their numbers). */
+int th_plan(uint32_t alg, uint64_t len, uint64_t stride, uint32_t n, char* out, size_t cap);
 
 #ifdef __cplusplus
 }

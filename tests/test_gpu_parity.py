@@ -233,6 +233,23 @@ def test_fused_verify_through_submit_mixed_lengths(eng):
     assert (out[MD5] == ref_digests(MD5, bufs)).all()
 
 
+def test_submit_uniform_prefix_plus_short_last_piece(eng):
+    """A torrent's pieces: all equal but the last.  th_submit sends the equal-length prefix to the
+    tensor-map kernels and the remainder to the per-lane path; digests and bitfield must line up."""
+    rng = np.random.default_rng(17)
+    for n_full, ln, tail in [(100, 8192, [100]), (64, 16384, []), (333, 4096, [4095, 17, 0]), (96, 2048, [2048 + 64])]:
+        lens = [ln] * n_full + tail
+        bufs = [rng.integers(0, 256, x, dtype=np.uint8) for x in lens]
+        exp = ref_digests(SHA1, bufs).copy()
+        bad = sorted({0, 31, 32, n_full - 1, len(lens) - 1})
+        for b in bad:
+            exp[b, 7] ^= 2
+        out = eng.hash_batch(bufs, SHA1 | MD5 | SHA256, expected_sha1=exp)
+        assert sorted(np.nonzero(~out["ok"])[0].tolist()) == bad, (n_full, ln, tail)
+        for a in (SHA1, MD5, SHA256):
+            assert (out[a] == ref_digests(a, bufs)).all(), (NAMES[a], n_full, ln, tail)
+
+
 def test_etag_combine_vs_oracle(eng, kat):
     rng = np.random.default_rng(9)
     counts = [1, 2, 3, 4, 5, 7, 8, 9, 64, 1000, 10000, 0]
