@@ -27,6 +27,16 @@ __device__ __forceinline__ uint32_t rotl(uint32_t x, int n) { return __funnelshi
 __device__ __forceinline__ uint32_t rotr(uint32_t x, int n) { return __funnelshift_r(x, x, n); }
 __device__ __forceinline__ uint32_t bswap(uint32_t x) { return __byte_perm(x, 0, 0x0123); }
 
+// a + b issued as IMAD on the FMA pipe instead of IADD3 on the (saturated) ALU pipe.  `one` is the
+// kernel argument 1: a literal would be folded back into an add.  The alu pipe issues one warp
+// instruction every 2 cycles per sub-partition and so does the fma pipe, so adds moved here run
+// beside the LOP3/SHF work for free (B300_MICROARCH.md "Pipe rates").
+__device__ __forceinline__ uint32_t add_fma(uint32_t a, uint32_t b, uint32_t one) {
+  uint32_t r;
+  asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(one), "r"(b));
+  return r;
+}
+
 constexpr int LUT_CH = 0xCA;   // (a & b) | (~a & c)
 constexpr int LUT_MAJ = 0xE8;  // majority
 constexpr int LUT_XOR3 = 0x96; // a ^ b ^ c
@@ -40,7 +50,7 @@ struct Sha1 {
     h[0] = 0x67452301u; h[1] = 0xefcdab89u; h[2] = 0x98badcfeu; h[3] = 0x10325476u; h[4] = 0xc3d2e1f0u;
   }
   // w: 16 big-endian-decoded words; used as the rolling schedule window (destroyed).
-  __device__ static __forceinline__ void compress(uint32_t* h, uint32_t* w) {
+  __device__ static __forceinline__ void compress(uint32_t* h, uint32_t* w, uint32_t one) {
     uint32_t a = h[0], b = h[1], c = h[2], d = h[3], e = h[4];
 #pragma unroll
     for (int t = 0; t < 80; t++) {
@@ -51,8 +61,12 @@ struct Sha1 {
       else if (t < 40) { f = lop3<LUT_XOR3>(b, c, d); k = 0x6ed9eba1u; }
       else if (t < 60) { f = lop3<LUT_MAJ>(b, c, d);  k = 0x8f1bbcdcu; }
       else             { f = lop3<LUT_XOR3>(b, c, d); k = 0xca62c1d6u; }
-      uint32_t ekw = e + k + w[t & 15];       // off the critical path
-      uint32_t tmp = rotl(a, 5) + f + ekw;
+      // x = f + e + K + W[t] is off the critical path (f uses a from two rounds back): three IMADs;
+      // the round's only dependent op is rotl(a,5) + x, which ptxas fuses into one LEA.HI
+      uint32_t x = add_fma(w[t & 15], k, one);
+      x = add_fma(e, x, one);
+      x = add_fma(f, x, one);
+      uint32_t tmp = rotl(a, 5) + x;
       e = d; d = c; c = rotl(b, 30); b = a; a = tmp;
     }
     h[0] += a; h[1] += b; h[2] += c; h[3] += d; h[4] += e;
@@ -68,7 +82,7 @@ struct Md5 {
   }
   template <int I>
   __device__ static __forceinline__ void step(uint32_t& a, uint32_t b, uint32_t c, uint32_t d,
-                                              const uint32_t* m) {
+                                              const uint32_t* m, uint32_t one) {
     constexpr uint32_t T[64] = {
         0xd76aa478, 0xe8c7b756, 0x242070db, 0xc1bdceee, 0xf57c0faf, 0x4787c62a, 0xa8304613, 0xfd469501,
         0x698098d8, 0x8b44f7af, 0xffff5bb1, 0x895cd7be, 0x6b901122, 0xfd987193, 0xa679438e, 0x49b40821,
@@ -85,24 +99,27 @@ struct Md5 {
                  : R == 1 ? lop3<LUT_CH>(d, b, c)
                  : R == 2 ? lop3<LUT_XOR3>(b, c, d)
                           : lop3<LUT_MD5I>(b, c, d);
+    // plain adds: ptxas already splits them between IADD3 / IMAD.IADD and fuses rotl(...) + b into
+    // one LEA.HI (4 instructions per step); forcing every add onto the FMA pipe measured slower here
+    (void)one;
     uint32_t akm = a + T[I] + m[G];  // off the critical path
     a = b + rotl(akm + f, S[(R << 2) | (I & 3)]);
   }
   template <int I>
   __device__ static __forceinline__ void four(uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d,
-                                              const uint32_t* m) {
-    step<I>(a, b, c, d, m);
-    step<I + 1>(d, a, b, c, m);
-    step<I + 2>(c, d, a, b, m);
-    step<I + 3>(b, c, d, a, m);
+                                              const uint32_t* m, uint32_t one) {
+    step<I>(a, b, c, d, m, one);
+    step<I + 1>(d, a, b, c, m, one);
+    step<I + 2>(c, d, a, b, m, one);
+    step<I + 3>(b, c, d, a, m, one);
   }
   // w: 16 little-endian words (not modified).
-  __device__ static __forceinline__ void compress(uint32_t* h, const uint32_t* m) {
+  __device__ static __forceinline__ void compress(uint32_t* h, const uint32_t* m, uint32_t one) {
     uint32_t a = h[0], b = h[1], c = h[2], d = h[3];
-    four<0>(a, b, c, d, m);  four<4>(a, b, c, d, m);  four<8>(a, b, c, d, m);  four<12>(a, b, c, d, m);
-    four<16>(a, b, c, d, m); four<20>(a, b, c, d, m); four<24>(a, b, c, d, m); four<28>(a, b, c, d, m);
-    four<32>(a, b, c, d, m); four<36>(a, b, c, d, m); four<40>(a, b, c, d, m); four<44>(a, b, c, d, m);
-    four<48>(a, b, c, d, m); four<52>(a, b, c, d, m); four<56>(a, b, c, d, m); four<60>(a, b, c, d, m);
+    four<0>(a, b, c, d, m, one);  four<4>(a, b, c, d, m, one);  four<8>(a, b, c, d, m, one);  four<12>(a, b, c, d, m, one);
+    four<16>(a, b, c, d, m, one); four<20>(a, b, c, d, m, one); four<24>(a, b, c, d, m, one); four<28>(a, b, c, d, m, one);
+    four<32>(a, b, c, d, m, one); four<36>(a, b, c, d, m, one); four<40>(a, b, c, d, m, one); four<44>(a, b, c, d, m, one);
+    four<48>(a, b, c, d, m, one); four<52>(a, b, c, d, m, one); four<56>(a, b, c, d, m, one); four<60>(a, b, c, d, m, one);
     h[0] += a; h[1] += b; h[2] += c; h[3] += d;
   }
 };
@@ -115,7 +132,7 @@ struct Sha256 {
     h[0] = 0x6a09e667u; h[1] = 0xbb67ae85u; h[2] = 0x3c6ef372u; h[3] = 0xa54ff53au;
     h[4] = 0x510e527fu; h[5] = 0x9b05688cu; h[6] = 0x1f83d9abu; h[7] = 0x5be0cd19u;
   }
-  __device__ static __forceinline__ void compress(uint32_t* h, uint32_t* w) {
+  __device__ static __forceinline__ void compress(uint32_t* h, uint32_t* w, uint32_t one) {
     constexpr uint32_t K[64] = {
         0x428a2f98, 0x71374491, 0xb5c0fbcf, 0xe9b5dba5, 0x3956c25b, 0x59f111f1, 0x923f82a4, 0xab1c5ed5,
         0xd807aa98, 0x12835b01, 0x243185be, 0x550c7dc3, 0x72be5d74, 0x80deb1fe, 0x9bdc06a7, 0xc19bf174,
@@ -132,14 +149,16 @@ struct Sha256 {
         uint32_t x = w[(t - 15) & 15], y = w[(t - 2) & 15];
         uint32_t s0 = lop3<LUT_XOR3>(rotr(x, 7), rotr(x, 18), x >> 3);
         uint32_t s1 = lop3<LUT_XOR3>(rotr(y, 17), rotr(y, 19), y >> 10);
-        w[t & 15] = w[t & 15] + s0 + w[(t - 7) & 15] + s1;
+        w[t & 15] = add_fma(add_fma(w[t & 15], s0, one), add_fma(w[(t - 7) & 15], s1, one), one);
       }
+      // every add goes to the FMA pipe as IMAD; the ALU pipe keeps only the rotates and booleans
       uint32_t S1 = lop3<LUT_XOR3>(rotr(e, 6), rotr(e, 11), rotr(e, 25));
-      uint32_t t1 = hh + K[t] + w[t & 15];  // off the critical path
-      t1 = t1 + S1 + lop3<LUT_CH>(e, f, g);
+      uint32_t t1 = add_fma(w[t & 15], K[t], one);  // off the critical path
+      t1 = add_fma(hh, t1, one);
+      t1 = add_fma(add_fma(S1, lop3<LUT_CH>(e, f, g), one), t1, one);
       uint32_t S0 = lop3<LUT_XOR3>(rotr(a, 2), rotr(a, 13), rotr(a, 22));
-      uint32_t t2 = S0 + lop3<LUT_MAJ>(a, b, c);
-      hh = g; g = f; f = e; e = d + t1; d = c; c = b; b = a; a = t1 + t2;
+      uint32_t t2 = add_fma(S0, lop3<LUT_MAJ>(a, b, c), one);
+      hh = g; g = f; f = e; e = add_fma(d, t1, one); d = c; c = b; b = a; a = add_fma(t1, t2, one);
     }
     h[0] += a; h[1] += b; h[2] += c; h[3] += d; h[4] += e; h[5] += f; h[6] += g; h[7] += hh;
   }
@@ -237,7 +256,7 @@ struct Staging {
 // smem: this warp's Staging<CH,NST>::WARP_BYTES region (16-byte aligned).
 template <class A, int CH, int NST>
 __device__ __forceinline__ void digest_stream(const uint8_t* __restrict__ msg, uint64_t len, uint32_t* h,
-                                              unsigned char* smem, int lane) {
+                                              unsigned char* smem, int lane, uint32_t one) {
   using G = Staging<CH, NST>;
   constexpr unsigned FULL = 0xffffffffu;
   const uint32_t s_base = smem_u32(smem);
@@ -303,7 +322,7 @@ __device__ __forceinline__ void digest_stream(const uint8_t* __restrict__ msg, u
 #pragma unroll
           for (int i = 0; i < 16; i++) w[i] = bswap(w[i]);
         }
-        A::compress(h, w);
+        A::compress(h, w, one);
       }
     }
     __syncwarp();
@@ -354,7 +373,7 @@ struct PipeState {
 template <class A, int K, int NST>
 __device__ __forceinline__ void tile_segment(const void* tmap, uint32_t row0, uint64_t len, uint32_t c_begin,
                                              uint32_t c_end, uint32_t nch, uint32_t* h, uint32_t s_tiles,
-                                             uint32_t s_bar, int lane, PipeState& ps) {
+                                             uint32_t s_bar, int lane, PipeState& ps, uint32_t one) {
   using G = Tiles<K, NST>;
   constexpr int CH = G::CH;
   auto issue = [&](uint32_t c, int s) {
@@ -402,7 +421,7 @@ __device__ __forceinline__ void tile_segment(const void* tmap, uint32_t row0, ui
 #pragma unroll
         for (int i = 0; i < 16; i++) w[i] = bswap(w[i]);
       }
-      A::compress(h, w);
+      A::compress(h, w, one);
     }
     __syncwarp();
     fence_proxy_async_smem();

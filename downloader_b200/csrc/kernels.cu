@@ -28,6 +28,7 @@ struct DigestArgs {
   uint8_t* out;
   const uint8_t* expected;  // SHA-1 only, nullable
   uint32_t* ok_bits;        // SHA-1 only, nullable
+  uint32_t one;             // the value 1, opaque to the compiler (see add_fma)
 };
 
 template <class A, int CH, int NST>
@@ -44,7 +45,7 @@ __global__ void __launch_bounds__(32) digest_kernel(const DigestArgs p) {
     len = p.lengths ? p.lengths[idx] : p.len;
   }
   uint32_t h[A::NS];
-  digest_stream<A, CH, NST>(p.base + off, len, h, smem, lane);
+  digest_stream<A, CH, NST>(p.base + off, len, h, smem, lane, p.one);
   if (valid) store_digest<A>(p.out + (size_t)idx * A::DLEN, h);
 
   if (A::DLEN == 20 && p.expected && p.ok_bits) {  // fused piece verification
@@ -73,6 +74,7 @@ struct TileArgs {
   uint8_t* out;
   const uint8_t* expected;  // SHA-1 only, nullable
   uint32_t* ok_bits;        // SHA-1 only, nullable
+  uint32_t one;             // the value 1, opaque to the compiler (see add_fma)
 };
 
 template <class A>
@@ -113,7 +115,7 @@ __global__ void __launch_bounds__(32) digest_tile_kernel(const __grid_constant__
   uint32_t h[A::NS];
   A::init(h);
   PipeState ps;
-  tile_segment<A, K, NST>(&tmap, blockIdx.x * 32u, p.len, 0u, nch, nch, h, s_tiles, s_bar, lane, ps);
+  tile_segment<A, K, NST>(&tmap, blockIdx.x * 32u, p.len, 0u, nch, nch, h, s_tiles, s_bar, lane, ps, p.one);
   finish_group<A>(p, blockIdx.x, lane, h);
 }
 
@@ -171,7 +173,7 @@ __global__ void __launch_bounds__(512, 1) digest_sliced_kernel(const __grid_cons
     }
     const uint32_t c_begin = seg * p.segc;
     const uint32_t c_end = min(nch, c_begin + p.segc);
-    tile_segment<A, K, NST>(&tmap, (g0 + g) * 32u, p.len, c_begin, c_end, nch, h, s_tiles, s_bar, lane, ps);
+    tile_segment<A, K, NST>(&tmap, (g0 + g) * 32u, p.len, c_begin, c_end, nch, h, s_tiles, s_bar, lane, ps, p.one);
     if (seg == S - 1) {
       finish_group<A>(p, g0 + g, lane, h);
     } else {
@@ -197,7 +199,7 @@ struct Md5Shfl {
     constexpr int G = R == 0 ? I : R == 1 ? (5 * I + 1) & 15 : R == 2 ? (3 * I + 5) & 15 : (7 * I) & 15;
     uint32_t m[16];
     m[G] = __shfl_sync(0xffffffffu, mine, half * 16 + G);
-    Md5::step<I>(a, b, c, d, m);
+    Md5::step<I>(a, b, c, d, m, 1u);
   }
   template <int I>
   __device__ static __forceinline__ void four(uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d, uint32_t mine,
@@ -428,7 +430,7 @@ static int launch_uniform(int ai, const void* d_base, uint64_t stride, uint64_t 
   if (pl.path == 1) return 1;
   CUtensorMap tmap;
   if (!make_tmap(&tmap, d_base, len, stride, n)) return 1;
-  TileArgs a{len, n, pl.segc, pl.nseg, d_out, d_expected, d_ok_bits};
+  TileArgs a{len, n, pl.segc, pl.nseg, d_out, d_expected, d_ok_bits, 1u};
   const TileVariant& v = g_tile_variants[pl.path == 3 ? g_sliced_selected[ai] : g_tile_selected[ai]];
   cudaError_t e = pl.path == 3 ? v.sliced[ai](tmap, a, pl.grid, pl.block, pl.smem, st)
                                : v.tile[ai](tmap, a, pl.grid, 32, 0, st);
@@ -464,7 +466,7 @@ static int launch_digest(uint32_t alg, const void* d_base, const uint64_t* d_off
     if (rc <= 0) return rc;
   }
   DigestArgs a{static_cast<const uint8_t*>(d_base), d_offsets, d_lengths, d_order, stride, len, n, d_out,
-               d_expected, d_ok_bits};
+               d_expected, d_ok_bits, 1u};
   cudaError_t e = g_variants[g_selected[ai]].fn[ai](a, static_cast<cudaStream_t>(stream));
   return e == cudaSuccess ? TH_OK : TH_ECUDA;
 }
