@@ -91,6 +91,7 @@ def lib() -> C.CDLL:
     L.th_sha256_batch.argtypes = [vp, vp, vp, vp, u64, u64, u32, vp, vp]
     L.th_etag_combine_device.argtypes = [vp, vp, u32, vp, vp]
     L.th_synth_fill.argtypes = [vp, u64, u64, u64, u64, u64, vp]
+    L.th_digest_ragged_static.argtypes = [u32, vp, vp, vp, u32, vp, vp, vp, vp]
     L.th_set_staging.argtypes = [u32, i32, i32]
     L.th_get_staging.argtypes = [u32, C.POINTER(i32), C.POINTER(i32)]
     L.th_set_tiling.argtypes = [u32, i32, i32]

@@ -471,6 +471,64 @@ static int launch_digest(uint32_t alg, const void* d_base, const uint64_t* d_off
   return e == cudaSuccess ? TH_OK : TH_ECUDA;
 }
 
+// ------------------------------------------------------------------- allocation-free ragged batches
+// Scratch for th_digest_ragged_static: lives in the library image, one copy per GPU that loads it,
+// until the process exits.  Host code may not treat `g_static_scratch` as a device address — it is
+// only a handle here; the real address comes from cudaGetSymbolAddress (static_scratch_ptr below).
+constexpr uint32_t kLenClasses = 128;  // 4 classes per power of two of the block count
+struct StaticScratch {
+  uint32_t count[kLenClasses];   // messages per length class      (zeroed at the start of every call)
+  uint32_t cursor[kLenClasses];  // next free place in each class   (zeroed at the start of every call)
+  uint32_t order[TH_STATIC_MAX_MSGS];  // thread slot -> message index, longest classes first
+};
+static __device__ __align__(256) unsigned char g_static_scratch[sizeof(StaticScratch)];
+
+__device__ __forceinline__ uint32_t len_class(uint64_t len) {
+  const uint64_t blocks = (len >> 6) + 1;                     // >= 1
+  const int e = 63 - __clzll((long long)blocks);              // floor(log2(blocks)), 0..58
+  const uint32_t frac = e >= 2 ? (uint32_t)((blocks >> (e - 2)) & 3u) : (uint32_t)((blocks << (2 - e)) & 3u);
+  const uint32_t c = (uint32_t)e * 4u + frac;
+  return c < kLenClasses ? c : kLenClasses - 1;
+}
+
+__global__ void __launch_bounds__(256) class_count_kernel(const uint64_t* __restrict__ lengths, uint32_t n,
+                                                          StaticScratch* s) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) atomicAdd(&s->count[len_class(lengths[i])], 1u);
+}
+
+__global__ void __launch_bounds__(256) class_place_kernel(const uint64_t* __restrict__ lengths, uint32_t n,
+                                                          StaticScratch* s) {
+  __shared__ uint32_t base[kLenClasses];
+  if (threadIdx.x == 0) {  // longest class first
+    uint32_t acc = 0;
+    for (int c = (int)kLenClasses - 1; c >= 0; c--) { base[c] = acc; acc += s->count[c]; }
+  }
+  __syncthreads();
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const uint32_t c = len_class(lengths[i]);
+    s->order[base[c] + atomicAdd(&s->cursor[c], 1u)] = i;
+  }
+}
+
+// Device address of the scratch array for the current device, looked up once per device.
+static cudaError_t static_scratch_ptr(StaticScratch** out) {
+  static StaticScratch* cached[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+  if (!cached[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess) return e;
+    cached[dev] = static_cast<StaticScratch*>(p);
+  }
+  *out = cached[dev];
+  return cudaSuccess;
+}
+
 }  // namespace th
 
 // ----------------------------------------------------------------------------------------- C ABI
@@ -518,6 +576,27 @@ int th_synth_fill(void* d_dst, uint64_t first_msg, uint64_t n, uint64_t len, uin
   th::synth_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<uint8_t*>(d_dst), first_msg, n, len, stride, seed);
   return cudaGetLastError() == cudaSuccess ? TH_OK : TH_ECUDA;
+}
+
+int th_digest_ragged_static(uint32_t alg, const void* d_base, const uint64_t* d_offsets, const uint64_t* d_lengths,
+                            uint32_t n, uint8_t* d_out, const uint8_t* d_expected20, uint32_t* d_ok_bits,
+                            void* stream) {
+  if (th::alg_index(alg) < 0 || !d_out || !d_offsets || !d_lengths) return TH_EINVAL;
+  if (n > TH_STATIC_MAX_MSGS) return TH_ETOOBIG;  // the built-in scratch holds TH_STATIC_MAX_MSGS slots
+  if (n == 0) return TH_OK;
+  th::StaticScratch* s = nullptr;
+  if (th::static_scratch_ptr(&s) != cudaSuccess) return TH_ECUDA;  // first call on this device: symbol lookup
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // the array still holds the previous call's counters: they must start from zero
+  if (cudaMemsetAsync(s, 0, 2 * th::kLenClasses * sizeof(uint32_t), st) != cudaSuccess) return TH_ECUDA;
+  const bool verify = alg == TH_ALG_SHA1 && d_expected20 && d_ok_bits;
+  if (verify && cudaMemsetAsync(d_ok_bits, 0, ((n + 31u) / 32u) * 4u, st) != cudaSuccess) return TH_ECUDA;
+  const uint32_t blocks = (n + 255u) / 256u;
+  th::class_count_kernel<<<blocks, 256, 0, st>>>(d_lengths, n, s);
+  th::class_place_kernel<<<blocks, 256, 0, st>>>(d_lengths, n, s);
+  if (cudaGetLastError() != cudaSuccess) return TH_ECUDA;
+  return th::launch_digest(alg, d_base, d_offsets, d_lengths, s->order, 0, 0, n, d_out,
+                           verify ? d_expected20 : nullptr, verify ? d_ok_bits : nullptr, stream);
 }
 
 int th_set_staging(uint32_t alg, int chunk_bytes, int stages) {

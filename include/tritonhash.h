@@ -148,6 +148,28 @@ int th_etag_combine_device(const uint8_t* d_md5s, const uint64_t* d_part_prefix,
 int th_synth_fill(void* d_dst, uint64_t first_msg, uint64_t n, uint64_t len, uint64_t stride,
                   uint64_t seed, void* stream);
 
+/* No counterpart in the reference.  Ragged batch (pieces / parts of unlike lengths) for callers that
+ * must not allocate: every other way into the ragged path (th_submit, th_submit_device) builds its
+ * length-bucketing table in device memory the library obtains with cudaMalloc / cudaHostAlloc, and an
+ * allocation synchronises the whole device and fails outright when the application has already given
+ * all of HBM to its own pools or rings — which is exactly the situation of a plug-in called from a
+ * media pipeline's callback, or of the N-API add-on once its rings are sized to fill the GPU.
+ * This entry point sorts the messages into length classes on the GPU, in a table that is part of the
+ * library image (about 257 KiB of device memory per GPU, held until the process exits), and then runs
+ * the same digest kernel th_sha1_batch / th_md5_batch / th_sha256_batch run; it calls no allocator.
+ *   - at most TH_STATIC_MAX_MSGS messages per call; more is refused with TH_ETOOBIG;
+ *   - alg is one of TH_ALG_*; d_offsets / d_lengths / d_out (/ d_expected20, d_ok_bits for SHA-1
+ *     verification) are device pointers as in the launch-level calls; d_ok_bits is cleared here;
+ *   - the first call on each device looks up the table's device address (cudaGetSymbolAddress) with
+ *     that device current; make that first call before you start capturing the stream;
+ *   - all calls on a device share the one table, which keeps what the last call left in it: the
+ *     counters are cleared at the start of each call, and two calls whose work overlaps on the GPU
+ *     (different streams) race on it — serialise them. */
+#define TH_STATIC_MAX_MSGS 65536u
+int th_digest_ragged_static(uint32_t alg, const void* d_base, const uint64_t* d_offsets,
+                            const uint64_t* d_lengths, uint32_t n, uint8_t* d_out,
+                            const uint8_t* d_expected20, uint32_t* d_ok_bits, void* stream);
+
 /* Staging geometry of the digest kernels: bytes each lane stages per pipeline stage (multiple of
  * 64, 64..1024) and the number of stages (2..4).  Process-wide; returns TH_EINVAL if no such
  * variant was compiled.  Defaults are the tuned values in DESIGN.md. */
