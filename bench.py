@@ -294,6 +294,11 @@ def main():
     if not args.skip_e2e:
         slots = args.e2e_slots
         per_slot = n // slots
+        # pinned-memory budget: never ask for more than ~45 % of the host's available RAM over all ranks
+        avail = _mem_available()
+        budget = int(0.45 * avail / world) if avail else total_bytes
+        while per_slot > 32 and slots * per_slot * ln > budget:
+            per_slot //= 2
         slot_bytes = per_slot * ln
         eng = Engine([local], ring_bytes=slots * slot_bytes)
         mask = ALG_SHA1 if algs == "sha1" else (ALG_MD5 | ALG_SHA256)
@@ -350,7 +355,7 @@ def main():
         e2e = {"value": round(world * slots * slot_bytes / dt / GB, 3), "unit": "GB/s",
                "h2d_bytes_per_step": int((s1["h2d_bytes"] - s0["h2d_bytes"]) // e2e_steps),
                "d2h_bytes_per_step": int((s1["d2h_bytes"] - s0["d2h_bytes"]) // e2e_steps),
-               "steps": e2e_steps, "ms_per_step": round(dt * 1e3, 3), "timing": "host wall clock around submit..result, max over ranks",
+               "messages_per_gpu": slots * per_slot, "steps": e2e_steps, "ms_per_step": round(dt * 1e3, 3), "timing": "host wall clock around submit..result, max over ranks",
                "launches_per_step": int((s1["launches"] - s0["launches"]) // e2e_steps),
                "kernel_ms_per_step": round((s1["kernel_ms"] - s0["kernel_ms"]) / e2e_steps, 3)}
         eng.close()
@@ -405,6 +410,17 @@ def main():
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
+    return 0
+
+
+def _mem_available():
+    try:
+        with open("/proc/meminfo") as f:
+            for line in f:
+                if line.startswith("MemAvailable:"):
+                    return int(line.split()[1]) * 1024
+    except OSError:
+        pass
     return 0
 
 
