@@ -119,6 +119,35 @@ __global__ void __launch_bounds__(32) digest_tile_kernel(const __grid_constant__
   finish_group<A>(p, blockIdx.x, lane, h);
 }
 
+// Few, large messages (fewer groups than SM sub-partitions): chain warp + schedule helper warp per group.
+template <class A, int K, int NST, int SS>
+__global__ void __launch_bounds__(64) digest_assist_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs p) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  using G = Tiles<K, NST>;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t s_tiles = smem_u32(smem);
+  const uint32_t s_ring = s_tiles + G::WARP_BYTES;
+  const uint32_t s_bar = s_ring + SS * Assist<A>::WPB * 128;
+  if (threadIdx.x == 32) {
+    prefetch_tmap(&tmap);
+#pragma unroll
+    for (int s = 0; s < NST; s++) mbar_init(s_bar + 8 * s, 1);
+    mbar_init_fence();
+  }
+  __syncthreads();
+  const uint32_t nch = (uint32_t)(p.len / G::CH) + 1u;
+  const uint32_t r = (uint32_t)(p.len & 63u);
+  const uint32_t total = (uint32_t)(p.len >> 6) + (r < 56 ? 1u : 2u);
+  if (warp == 1) {
+    assist_produce<A, K, NST, SS>(&tmap, blockIdx.x * 32u, p.len, nch, s_tiles, s_bar, s_ring, lane, p.one);
+  } else {
+    uint32_t h[A::NS];
+    A::init(h);
+    assist_consume<A, SS>(total, h, smem + G::WARP_BYTES, lane, p.one);
+    finish_group<A>(p, blockIdx.x, lane, h);
+  }
+}
+
 // Persistent, time-sliced: one CTA per SM, W worker warps (a multiple of 4, so every SM sub-partition
 // holds the same number), G = this SM's share of the message groups.  A chain cannot be split across
 // threads, but it can be handed from warp to warp between blocks: its whole state is the chaining value.
@@ -325,7 +354,9 @@ static bool make_tmap(CUtensorMap* m, const void* base, uint64_t len, uint64_t s
 }
 
 struct TileOpts {
-  int path = 0;        // 0 auto, 1 per-lane bulk copies (any layout), 2 tile kernel, 3 sliced kernel
+  int path = 0;        // 0 auto, 1 per-lane bulk copies (any layout), 2 tile kernel, 3 sliced kernel, 4 assist kernel
+  int assist_variant = 0;       // tuning: which (tiles, stages, ring slots) instantiation path 4 uses
+  int assist_max_groups = 296;  // auto: chain + helper warp per group while two sub-partitions per group exist
   int workers = 12;    // sliced kernel: worker warps per SM (multiple of 4)
   int rounds = 32;     // sliced kernel: target scheduling rounds (units per worker)
   int sliced_min_groups = 592;  // auto: use the sliced kernel from this many 32-message groups
@@ -358,6 +389,19 @@ cudaError_t launch_sliced(const CUtensorMap& m, const TileArgs& a, uint32_t grid
     set_to[dev] = 227 * 1024;
   }
   digest_sliced_kernel<A, K, NST><<<grid, block, smem, st>>>(m, a);
+  return cudaGetLastError();
+}
+
+template <class A, int K, int NST, int SS>
+cudaError_t launch_assist(const CUtensorMap& m, const TileArgs& a, uint32_t grid, uint32_t, size_t, cudaStream_t st) {
+  constexpr int smem = Tiles<K, NST>::WARP_BYTES + SS * Assist<A>::WPB * 128 + 8 * NST;
+  static bool set = false;
+  if (!set) {
+    cudaError_t e = cudaFuncSetAttribute(digest_assist_kernel<A, K, NST, SS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    set = true;
+  }
+  digest_assist_kernel<A, K, NST, SS><<<grid, 64, smem, st>>>(m, a);
   return cudaGetLastError();
 }
 
@@ -417,6 +461,11 @@ static Plan make_plan(int ai, uint64_t stride, uint64_t len, uint32_t n) {
     }
     // chaining-value slots do not fit beside the tiles: use the one-warp-per-CTA kernel
   }
+  if (ai != 1 && (g_opts.path == 4 || (g_opts.path == 0 && groups <= (uint32_t)g_opts.assist_max_groups))) {
+    pl.path = 4; pl.k = 2; pl.nst = 2; pl.grid = groups; pl.block = 64;
+    pl.smem = (size_t)2 * 2 * 4096 + 4 * (ai == 0 ? 80 : 64) * 128 + 16;
+    return pl;
+  }
   const TileVariant& v = g_tile_variants[g_tile_selected[ai]];
   pl.path = 2; pl.k = v.k; pl.nst = v.nst; pl.grid = groups; pl.block = 32;
   pl.smem = (size_t)v.k * v.nst * 4096 + 8 * v.nst;
@@ -431,6 +480,17 @@ static int launch_uniform(int ai, const void* d_base, uint64_t stride, uint64_t 
   CUtensorMap tmap;
   if (!make_tmap(&tmap, d_base, len, stride, n)) return 1;
   TileArgs a{len, n, pl.segc, pl.nseg, d_out, d_expected, d_ok_bits, 1u};
+  if (pl.path == 4) {
+    cudaError_t e;
+    switch (g_opts.assist_variant) {
+      case 1: e = ai == 0 ? launch_assist<Sha1, 4, 2, 4>(tmap, a, pl.grid, 64, 0, st) : launch_assist<Sha256, 4, 2, 4>(tmap, a, pl.grid, 64, 0, st); break;
+      case 2: e = ai == 0 ? launch_assist<Sha1, 4, 4, 4>(tmap, a, pl.grid, 64, 0, st) : launch_assist<Sha256, 4, 4, 4>(tmap, a, pl.grid, 64, 0, st); break;
+      case 3: e = ai == 0 ? launch_assist<Sha1, 4, 4, 7>(tmap, a, pl.grid, 64, 0, st) : launch_assist<Sha256, 4, 4, 7>(tmap, a, pl.grid, 64, 0, st); break;
+      case 4: e = ai == 0 ? launch_assist<Sha1, 2, 4, 2>(tmap, a, pl.grid, 64, 0, st) : launch_assist<Sha256, 2, 4, 2>(tmap, a, pl.grid, 64, 0, st); break;
+      default: e = ai == 0 ? launch_assist<Sha1, 2, 2, 4>(tmap, a, pl.grid, 64, 0, st) : launch_assist<Sha256, 2, 2, 4>(tmap, a, pl.grid, 64, 0, st); break;
+    }
+    return e == cudaSuccess ? TH_OK : TH_ECUDA;
+  }
   const TileVariant& v = g_tile_variants[pl.path == 3 ? g_sliced_selected[ai] : g_tile_selected[ai]];
   cudaError_t e = pl.path == 3 ? v.sliced[ai](tmap, a, pl.grid, pl.block, pl.smem, st)
                                : v.tile[ai](tmap, a, pl.grid, 32, 0, st);
@@ -613,7 +673,9 @@ int th_set_staging(uint32_t alg, int chunk_bytes, int stages) {
 int th_set_option(const char* name, long long value) {
   if (!name) return TH_EINVAL;
   const std::string k(name);
-  if (k == "path") { if (value < 0 || value > 3) return TH_EINVAL; th::g_opts.path = (int)value; return TH_OK; }
+  if (k == "path") { if (value < 0 || value > 4) return TH_EINVAL; th::g_opts.path = (int)value; return TH_OK; }
+  if (k == "assist_variant") { if (value < 0 || value > 4) return TH_EINVAL; th::g_opts.assist_variant = (int)value; return TH_OK; }
+  if (k == "assist_max_groups") { if (value < 0) return TH_EINVAL; th::g_opts.assist_max_groups = (int)value; return TH_OK; }
   if (k == "workers") { if (value < 4 || value > 16 || value % 4) return TH_EINVAL; th::g_opts.workers = (int)value; return TH_OK; }
   if (k == "rounds") { if (value < 1 || value > 4096) return TH_EINVAL; th::g_opts.rounds = (int)value; return TH_OK; }
   if (k == "sliced_min_groups") { if (value < 1) return TH_EINVAL; th::g_opts.sliced_min_groups = (int)value; return TH_OK; }
@@ -639,6 +701,10 @@ int th_plan(uint32_t alg, uint64_t len, uint64_t stride, uint32_t n, char* out, 
   if (pl.path == 1) {
     const th::Variant& v = th::g_variants[th::g_selected[ai]];
     snprintf(out, cap, "bulk: one-warp CTAs, per-lane cp.async.bulk, %d B x %d stages, grid %u", v.ch, v.nst, (n + 31u) / 32u);
+  } else if (pl.path == 4) {
+    snprintf(out, cap,
+             "assist: %u CTAs x (chain warp + schedule-helper warp), TMA 2-D {128B x 32 msgs} x %d tiles x %d stages, "
+             "4-slot schedule ring, smem %zu B", pl.grid, pl.k, pl.nst, pl.smem);
   } else if (pl.path == 2) {
     snprintf(out, cap, "tile: one-warp CTAs, TMA 2-D {128B x 32 msgs} x %d tiles x %d stages, grid %u, smem %zu B", pl.k,
              pl.nst, pl.grid, pl.smem);

@@ -161,6 +161,39 @@ def test_uniform_batch_paths_and_tilings(torch, L, path, k, nst):
         L.th_set_tiling(7, 1, 3)
 
 
+def test_assist_kernel_schedule_offload(torch, L):
+    """Few large messages: chain warp + schedule-helper warp per group (path 4, SHA-1 / SHA-256; MD5 has no
+    schedule and takes the tile kernel).  Lengths cover: fewer blocks than ring slots, exact block / tile /
+    stage multiples, both padding-block cases, a ragged last group."""
+    try:
+        assert L.th_set_option(b"path", 4) == 0
+        cases = [(5, 1024), (33, 1024 + 55), (40, 1024 + 56), (64, 2048), (7, 4096 + 63), (100, 65536 + 64), (3, (1 << 20) + 9)]
+        for n, ln in cases:
+            stride = (ln + 15) & ~15
+            d = torch.zeros(n * stride, dtype=torch.uint8, device="cuda")
+            assert L.th_synth_fill(d.data_ptr(), 0, n, ln, stride, 4242, None) == 0
+            outs = {a: torch.zeros(n * oracle.DIGEST_LEN[a], dtype=torch.uint8, device="cuda") for a in (SHA1, MD5, SHA256)}
+            ok = torch.full(((n + 31) // 32,), -1, dtype=torch.int32, device="cuda")
+            assert L.th_sha1_batch(d.data_ptr(), None, None, None, stride, ln, n, outs[SHA1].data_ptr(), None, None, None) == 0
+            exp = outs[SHA1].clone()
+            exp.view(n, 20)[n - 1, 2] ^= 8
+            assert L.th_sha1_batch(d.data_ptr(), None, None, None, stride, ln, n, outs[SHA1].data_ptr(), exp.data_ptr(), ok.data_ptr(), None) == 0
+            assert L.th_md5_batch(d.data_ptr(), None, None, None, stride, ln, n, outs[MD5].data_ptr(), None) == 0
+            assert L.th_sha256_batch(d.data_ptr(), None, None, None, stride, ln, n, outs[SHA256].data_ptr(), None) == 0
+            torch.cuda.synchronize()
+            host = d.cpu().numpy()
+            off = (np.arange(n) * stride).astype(np.uint64)
+            lens = np.full(n, ln, np.uint64)
+            for a in (SHA1, MD5, SHA256):
+                e = oracle.batch(a, host, off, lens, threads=8)
+                assert (outs[a].cpu().numpy().reshape(n, -1) == e).all(), (NAMES[a], n, ln)
+            words = ok.cpu().numpy().view(np.uint32)
+            bits = ((words[np.arange(n) >> 5] >> (np.arange(n) & 31)) & 1).astype(bool)
+            assert np.nonzero(~bits)[0].tolist() == [n - 1], (n, ln)
+    finally:
+        L.th_set_option(b"path", 0)
+
+
 def test_sliced_kernel_time_slicing_engaged(torch, L):
     """Config-2-like shape scaled down: ~14 groups per SM on 12 workers -> chains are cut into segments
     and handed between warps; result must not change."""

@@ -27,6 +27,7 @@ def main():
     ap.add_argument("--path", type=int, default=1, help="1 bulk (variants = CHxNST), 2 tile, 3 sliced (variants = KxNST)")
     ap.add_argument("--workers", default="12")
     ap.add_argument("--rounds", default="32")
+    ap.add_argument("--opt", default="", help="extra th_set_option pairs, e.g. assist_variant=2")
     a = ap.parse_args()
     L = _capi.lib()
     n, ln = a.n, a.len
@@ -35,6 +36,9 @@ def main():
     TILINGS = [(1, 2), (1, 3), (1, 4), (2, 2), (2, 3), (4, 2)]
     variants = (VARIANTS if a.path == 1 else TILINGS) if not a.variants else [tuple(map(int, v.split("x"))) for v in a.variants.split(",")]
     assert L.th_set_option(b"path", a.path) == 0
+    for kv in filter(None, a.opt.split(",")):
+        k, v = kv.split("=")
+        assert L.th_set_option(k.encode(), int(v)) == 0, kv
     combos = [(int(w), int(r)) for w in a.workers.split(",") for r in a.rounds.split(",")] if a.path == 3 else [(12, 32)]
     for alg in a.algs.split(","):
         out = torch.zeros(n * DL[alg], dtype=torch.uint8, device="cuda")
