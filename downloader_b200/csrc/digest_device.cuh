@@ -99,10 +99,10 @@ struct Md5 {
                  : R == 1 ? lop3<LUT_CH>(d, b, c)
                  : R == 2 ? lop3<LUT_XOR3>(b, c, d)
                           : lop3<LUT_MD5I>(b, c, d);
-    // plain adds: ptxas already splits them between IADD3 / IMAD.IADD and fuses rotl(...) + b into
-    // one LEA.HI (4 instructions per step); forcing every add onto the FMA pipe measured slower here
-    (void)one;
-    uint32_t akm = a + T[I] + m[G];  // off the critical path
+    // m[G] + T[I] depends on nothing in the chain: one IMAD on the FMA pipe.  The rest stays on the ALU pipe
+    // as IADD3 (a + mk + f) and LEA.HI (rotl + b): 3 ALU + 1 FMA instructions per step.  (All three adds as
+    // IMAD measured slower: the step's dependent chain got longer than three warps can hide.)
+    uint32_t akm = a + add_fma(m[G], T[I], one);
     a = b + rotl(akm + f, S[(R << 2) | (I & 3)]);
   }
   template <int I>

@@ -1,0 +1,58 @@
+#!/usr/bin/env python
+"""BASELINE config 5: message-size sweep, 4 KiB .. 64 MiB, per-GPU hashing GB/s against the integer roofline
+and the parallelism ceiling.  n = clamp(budget / size, 1024, 1Mi); budget defaults to
+16 GiB (the SURVEY's 64 GiB with --budget-gib 64).  Device-resident, auto kernel selection, CUDA events."""
+import argparse
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+
+from downloader_b200 import _capi
+
+ALG = {"sha1": 1, "md5": 2, "sha256": 4}
+DL = {"sha1": 20, "md5": 16, "sha256": 32}
+OPS = {"sha1": 613, "md5": 324, "sha256": 1400}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--budget-gib", type=int, default=16)
+    ap.add_argument("--algs", default="sha1,md5,sha256")
+    ap.add_argument("--iters", type=int, default=3)
+    a = ap.parse_args()
+    L = _capi.lib()
+    budget = a.budget_gib << 30
+    buf = torch.empty(budget, dtype=torch.uint8, device="cuda")
+    L.th_synth_fill(buf.data_ptr(), 0, budget // (1 << 20), 1 << 20, 1 << 20, 3, None)
+    for size in [4 << 10, 16 << 10, 64 << 10, 256 << 10, 1 << 20, 4 << 20, 16 << 20, 64 << 20]:
+        n = max(1024, min(1 << 20, budget // size))
+        n = min(n, budget // size)
+        for alg in a.algs.split(","):
+            out = torch.zeros(n * DL[alg], dtype=torch.uint8, device="cuda")
+            fn = {"sha1": lambda: L.th_sha1_batch(buf.data_ptr(), None, None, None, size, size, n, out.data_ptr(), None, None, None),
+                  "md5": lambda: L.th_md5_batch(buf.data_ptr(), None, None, None, size, size, n, out.data_ptr(), None),
+                  "sha256": lambda: L.th_sha256_batch(buf.data_ptr(), None, None, None, size, size, n, out.data_ptr(), None)}[alg]
+            iters = a.iters if n * size / 1e9 / 0.2 < 2 else 1
+            assert fn() == 0
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(iters):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / iters
+            gbps = n * size / ms / 1e6
+            roof = 148 * 64 * 1.965e9 / (OPS[alg] / 64.0) / 1e9
+            warps = (n + 31) // 32
+            print(json.dumps({"alg": alg, "message_bytes": size, "n": n, "ms": round(ms, 3), "GBps": round(gbps, 1),
+                              "frac_of_int_roofline": round(gbps / roof, 3),
+                              "parallelism_ceiling": round(min(1.0, warps / 592.0), 3),
+                              "kernel": _capi.plan(ALG[alg], size, size, n).split(":")[0]}), flush=True)
+
+
+if __name__ == "__main__":
+    main()
