@@ -33,7 +33,7 @@ struct DigestArgs {
 
 template <class A, int CH, int NST>
 __global__ void __launch_bounds__(32) digest_kernel(const DigestArgs p) {
-  extern __shared__ __align__(128) unsigned char smem[];
+  extern __shared__ __align__(1024) unsigned char smem[];
   const int lane = threadIdx.x;
   const uint32_t slot = blockIdx.x * 32u + lane;
   const bool valid = slot < p.n;
@@ -179,11 +179,12 @@ __global__ void __launch_bounds__(512, 1) digest_sliced_kernel(const __grid_cons
     for (int s = 0; s < NST; s++) mbar_init(s_bar + 8 * s, 1);
     mbar_init_fence();
   }
-  for (uint32_t g = threadIdx.x; g < G; g += blockDim.x) done[g] = 0;
+  const uint32_t S = p.nseg;
+  if (S > 1)
+    for (uint32_t g = threadIdx.x; g < G; g += blockDim.x) done[g] = 0;
   __syncthreads();
 
   const uint32_t nch = (uint32_t)(p.len / G_::CH) + 1u;
-  const uint32_t S = p.nseg;
   PipeState ps;
   const uint32_t units = G * S;
   for (uint32_t k = warp; k < units; k += W) {
@@ -417,8 +418,10 @@ constexpr int kNumTileVariants = sizeof(g_tile_variants) / sizeof(g_tile_variant
 static int g_tile_selected[3] = {5, 5, 5};    // one-warp CTAs: 4 tiles x 2 stages
 static int g_sliced_selected[3] = {3, 3, 3};  // persistent kernel: 2 tiles x 2 stages
 
-static size_t sliced_smem(int K, int NST, uint32_t W, uint32_t Gmax, int ns) {
-  return (size_t)W * K * NST * 4096 + ((W * 8 * NST + 127) & ~127u) + ((Gmax * 4 + 127) & ~127u) + (size_t)Gmax * ns * 128;
+// Chaining-value slots and hand-over counters are only needed when chains are cut into segments.
+static size_t sliced_smem(int K, int NST, uint32_t W, uint32_t Gmax, int ns, uint32_t S) {
+  const size_t base = (size_t)W * K * NST * 4096 + ((W * 8 * NST + 127) & ~127u);
+  return S > 1 ? base + ((Gmax * 4 + 127) & ~127u) + (size_t)Gmax * ns * 128 : base;
 }
 
 struct Plan {
@@ -453,7 +456,7 @@ static Plan make_plan(int ai, uint64_t stride, uint64_t len, uint32_t n) {
       if (S > smax) S = smax;
       if (S < 1) S = 1;
     }
-    const size_t smem = sliced_smem(v.k, v.nst, W, Gmax, ns);
+    const size_t smem = sliced_smem(v.k, v.nst, W, Gmax, ns, S);
     if (smem <= 227 * 1024) {
       pl.path = 3; pl.k = v.k; pl.nst = v.nst; pl.grid = grid; pl.block = W * 32; pl.workers = W;
       pl.segc = (nch + S - 1) / S; pl.nseg = (nch + pl.segc - 1) / pl.segc; pl.groups_per_cta = Gmax; pl.smem = smem;
