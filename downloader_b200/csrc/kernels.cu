@@ -360,6 +360,7 @@ struct TileOpts {
   int assist_max_groups = 296;  // auto: chain + helper warp per group while two sub-partitions per group exist
   int workers = 12;    // sliced kernel: worker warps per SM (multiple of 4)
   int rounds = 32;     // sliced kernel: target scheduling rounds (units per worker)
+  int slice_min_groups = 12;  // sliced kernel: cut chains into segments when a CTA has more groups than this
   int sliced_min_groups = 592;  // auto: use the sliced kernel from this many 32-message groups
 };
 static TileOpts g_opts;
@@ -450,7 +451,7 @@ static Plan make_plan(int ai, uint64_t stride, uint64_t len, uint32_t n) {
     const uint32_t Gmax = (groups + grid - 1) / grid;
     const uint32_t nch = (uint32_t)(len / (128u * v.k)) + 1u;
     uint32_t S = 1;
-    if (Gmax > W && Gmax < 4 * W) {  // few chains per worker: cut them so that ~rounds units run per worker
+    if (Gmax > (uint32_t)g_opts.slice_min_groups && Gmax < 4 * W) {  // few chains per worker: cut them so that ~rounds units run per worker
       S = ((uint32_t)g_opts.rounds * W + Gmax - 1) / Gmax;
       const uint32_t smax = nch / 4 ? nch / 4 : 1;  // at least 4 chunks per segment
       if (S > smax) S = smax;
@@ -680,6 +681,7 @@ int th_set_option(const char* name, long long value) {
   if (k == "assist_variant") { if (value < 0 || value > 4) return TH_EINVAL; th::g_opts.assist_variant = (int)value; return TH_OK; }
   if (k == "assist_max_groups") { if (value < 0) return TH_EINVAL; th::g_opts.assist_max_groups = (int)value; return TH_OK; }
   if (k == "workers") { if (value < 4 || value > 16 || value % 4) return TH_EINVAL; th::g_opts.workers = (int)value; return TH_OK; }
+  if (k == "slice_min_groups") { if (value < 0) return TH_EINVAL; th::g_opts.slice_min_groups = (int)value; return TH_OK; }
   if (k == "rounds") { if (value < 1 || value > 4096) return TH_EINVAL; th::g_opts.rounds = (int)value; return TH_OK; }
   if (k == "sliced_min_groups") { if (value < 1) return TH_EINVAL; th::g_opts.sliced_min_groups = (int)value; return TH_OK; }
   if (k == "tile_k" || k == "tile_stages") return TH_EINVAL;  // use th_set_tiling
