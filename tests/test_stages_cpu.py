@@ -1,0 +1,145 @@
+"""Host logic around the hot path, on CPU: the process filter (the reference's own three test cases,
+test/process/filter_dirs.js:17-82, on the same directory shapes), S3 framing, bencode, the reader's file
+concatenation, and the in-process S3 mock."""
+import asyncio
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from downloader_b200 import s3 as s3f
+from downloader_b200 import torrent as tor
+from downloader_b200.reader import _ConcatFiles, piece_bounds
+from downloader_b200.stages import Job, MediaType
+from downloader_b200.stages import process as process_stage
+from oracle.s3mock import S3Error, S3Mock
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+FIX = os.path.join(HERE, "fixtures", "filter_dirs")
+
+
+class MockLogger:
+    def info(self, *a): pass
+    def warn(self, *a): pass
+    def error(self, *a): pass
+    def debug(self, *a): pass
+
+
+def run(coro):
+    return asyncio.new_event_loop().run_until_complete(coro)
+
+
+@pytest.fixture()
+def processor():
+    return run(process_stage.factory({}, {}, MockLogger()))
+
+
+def test_should_filter_non_season_directories(processor):
+    base = os.path.join(FIX, "should_filter_non_season_directories")
+    res = run(processor(Job(lastStage={"path": base}, media={"id": "<uuid>", "type": MediaType.TV})))
+    assert len(res["files"]) == 2
+    assert res["files"][0] == os.path.join(base, "S1/KonoSuba S1E1.mkv")
+    assert res["downloadPath"] == base
+
+
+def test_should_read_all_dirs_when_processing_a_movie(processor):
+    base = os.path.join(FIX, "should_read_all_dirs_when_processing_a_movie")
+    res = run(processor(Job(lastStage={"path": base}, media={"id": "<uuid>", "type": MediaType.MOVIE})))
+    assert len(res["files"]) == 1
+    assert res["files"][0] == os.path.join(base, "Some Movie Dir/Your Name.mkv")
+
+
+def test_should_read_with_top_level_dir(processor):
+    base = os.path.join(FIX, "should_read_with_top_level_dir")
+    res = run(processor(Job(lastStage={"path": base}, media={"id": "<uuid>", "type": MediaType.TV})))
+    assert len(res["files"]) == 1
+    assert res["files"][0] == os.path.join(base, "Some Movie Dir/Your Name.mkv")
+
+
+def test_process_rejects_directories_without_media(processor, tmp_path):
+    (tmp_path / "a").mkdir()
+    (tmp_path / "b").mkdir()
+    (tmp_path / "a" / "x.txt").write_text("no media")
+    with pytest.raises(RuntimeError, match="Failed to find any suitable media files"):
+        run(processor(Job(lastStage={"path": str(tmp_path)}, media={"id": "x", "type": MediaType.TV})))
+
+
+def test_part_planning_matches_golden_and_oracle(kat):
+    for size, part in kat["framing"]["calc_part_size"]:
+        assert s3f.calculate_part_size(size) == part == oracle.calc_part_size(size)
+    assert s3f.calculate_part_size(1 << 30, 16 << 20, override=True) == 16 << 20
+    assert s3f.part_ranges(0, 64) == [(0, 0)]
+    r = s3f.part_ranges((1 << 30) + 5, 16 << 20)
+    assert len(r) == 65 and r[0] == (0, 16 << 20) and r[-1] == (1 << 30, (1 << 30) + 5)
+    p = s3f.plan_object(40 << 20, 16 << 20, override=True)
+    assert p.multipart and [e - s for s, e in p.ranges] == [16 << 20, 16 << 20, 8 << 20]
+    assert not s3f.plan_object(16 << 20, 16 << 20, override=True).multipart  # size <= partSize -> single PUT
+    with pytest.raises(ValueError):
+        s3f.calculate_part_size(s3f.MAX_OBJECT_SIZE + 1)
+
+
+def test_header_encodings_and_mode_selection(kat):
+    assert s3f.content_md5(hashlib.md5(b"abc").digest()) == kat["framing"]["content_md5_abc"]
+    assert s3f.sha256_hex(hashlib.sha256(b"abc").digest()) == hashlib.sha256(b"abc").hexdigest()
+    assert s3f.select_digests(anonymous=False, use_ssl=False) == 4   # plain HTTP + credentials -> SHA-256
+    assert s3f.select_digests(anonymous=False, use_ssl=True) == 2    # TLS -> Content-MD5
+    assert s3f.select_digests(anonymous=True, use_ssl=False) == 2
+    md5s = np.stack([np.frombuffer(hashlib.md5(bytes([i])).digest(), np.uint8) for i in range(3)])
+    listed = {1: '"' + hashlib.md5(bytes([0])).hexdigest() + '"', 3: "deadbeef"}
+    assert s3f.parts_to_skip(md5s, listed) == [1]
+
+
+def test_bencode_roundtrip_and_spans():
+    obj = {b"announce": b"http://t", b"info": {b"name": b"n", b"piece length": 16384, b"pieces": bytes(40), b"files": [
+        {b"length": 5, b"path": [b"a", b"b.mkv"]}, {b"length": 0, b"path": [b"c"]}]}, b"n": -7}
+    enc = tor.bencode(obj)
+    spans = {}
+    assert tor.bdecode(enc, spans) == obj
+    s, e = spans[(b"info",)]
+    assert enc[s:e] == tor.bencode(obj[b"info"])
+    for bad in (b"i12", b"5:abc", b"d3:fooe", b"le "):
+        with pytest.raises(ValueError):
+            tor.bdecode(bad)
+
+
+def test_concat_files_reads_across_boundaries(tmp_path):
+    sizes = [10, 0, 4097, 33]
+    blob = oracle.synth(1, sum(sizes)).tobytes()
+    files, pos = [], 0
+    for i, n in enumerate(sizes):
+        p = tmp_path / f"f{i}"
+        p.write_bytes(blob[pos:pos + n])
+        files.append((str(p), n))
+        pos += n
+    files.append((str(tmp_path / "missing"), 20))  # a file that is not there reads as zeros
+    src = _ConcatFiles(files)
+    try:
+        for start, ln in [(0, 10), (5, 100), (9, 4200), (0, sum(sizes) + 20), (4100, 60)]:
+            buf = np.full(ln, 0xEE, np.uint8)
+            src.readinto(buf, start)
+            exp = (blob + bytes(20))[start:start + ln]
+            assert buf.tobytes() == exp.ljust(ln, b"\0")
+    finally:
+        src.close()
+    assert piece_bounds(10, 4) == [(0, 4), (4, 8), (8, 10)]
+
+
+def test_s3_mock_plays_the_server():
+    m = S3Mock()
+    assert not m.bucketExists("b")
+    m.makeBucket("b")
+    body = b"true"
+    assert m.putObject("b", "k", body, {"Content-MD5": s3f.content_md5(hashlib.md5(body).digest())}) == hashlib.md5(body).hexdigest()
+    with pytest.raises(S3Error, match="BadDigest"):
+        m.putObject("b", "k", body, {"Content-MD5": s3f.content_md5(hashlib.md5(b"x").digest())})
+    with pytest.raises(S3Error, match="XAmzContentSHA256Mismatch"):
+        m.putObject("b", "k", body, {"x-amz-content-sha256": hashlib.sha256(b"x").hexdigest()})
+    with pytest.raises(S3Error, match="InvalidArgument"):
+        m.putObject("b", "k", body, {"x-amz-content-sha256": "abcd"})
+    uid = m.newMultipartUpload("b", "o")
+    parts = [b"a" * 100, b"b" * 50, b"c"]
+    etags = [m.putPart("b", "o", uid, i + 1, p, {"x-amz-content-sha256": hashlib.sha256(p).hexdigest()}) for i, p in enumerate(parts)]
+    et = m.completeMultipartUpload("b", "o", uid, etags)
+    assert et == oracle.etag_multipart(b"".join(hashlib.md5(p).digest() for p in parts))
