@@ -310,15 +310,8 @@ using launch_fn = cudaError_t (*)(const DigestArgs&, cudaStream_t);
 
 template <class A, int CH, int NST>
 cudaError_t launch_variant(const DigestArgs& a, cudaStream_t st) {
-  constexpr int smem = Staging<CH, NST>::WARP_BYTES;
-  static bool attr_set[64] = {};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (smem > 48 * 1024 && dev < 64 && !attr_set[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(digest_kernel<A, CH, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return e;
-    attr_set[dev] = true;
-  }
+  constexpr int smem = Staging<CH, NST>::WARP_BYTES;  // <= 34 KiB for every compiled variant: no opt-in needed
+  static_assert(smem <= 48 * 1024, "bulk staging variant needs the dynamic shared memory opt-in");
   const uint32_t grid = (a.n + 31u) / 32u;
   digest_kernel<A, CH, NST><<<grid, 32, smem, st>>>(a);
   return cudaGetLastError();
@@ -367,14 +360,28 @@ static TileOpts g_opts;
 
 using tile_fn = cudaError_t (*)(const CUtensorMap&, const TileArgs&, uint32_t grid, uint32_t block, size_t smem, cudaStream_t);
 
+// cudaFuncSetAttribute is per device: remember, per kernel instantiation, which devices have been set up.
+template <class KernelPtr>
+static cudaError_t allow_smem(KernelPtr kernel, bool* done /* [64] */, int bytes) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+  if (!done[dev]) {
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) return e;
+    done[dev] = true;
+  }
+  return cudaSuccess;
+}
+
 template <class A, int K, int NST>
 cudaError_t launch_tile(const CUtensorMap& m, const TileArgs& a, uint32_t grid, uint32_t, size_t, cudaStream_t st) {
   constexpr int smem = Tiles<K, NST>::WARP_BYTES + 8 * NST;
-  static bool set = false;
-  if (!set && smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(digest_tile_kernel<A, K, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  static bool done[64] = {};
+  if (smem > 48 * 1024) {
+    cudaError_t e = allow_smem(digest_tile_kernel<A, K, NST>, done, smem);
     if (e != cudaSuccess) return e;
-    set = true;
   }
   digest_tile_kernel<A, K, NST><<<grid, 32, smem, st>>>(m, a);
   return cudaGetLastError();
@@ -382,14 +389,9 @@ cudaError_t launch_tile(const CUtensorMap& m, const TileArgs& a, uint32_t grid, 
 
 template <class A, int K, int NST>
 cudaError_t launch_sliced(const CUtensorMap& m, const TileArgs& a, uint32_t grid, uint32_t block, size_t smem, cudaStream_t st) {
-  static size_t set_to[64] = {};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (dev < 64 && set_to[dev] < smem) {
-    cudaError_t e = cudaFuncSetAttribute(digest_sliced_kernel<A, K, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (e != cudaSuccess) return e;
-    set_to[dev] = 227 * 1024;
-  }
+  static bool done[64] = {};
+  cudaError_t e0 = allow_smem(digest_sliced_kernel<A, K, NST>, done, 227 * 1024);
+  if (e0 != cudaSuccess) return e0;
   digest_sliced_kernel<A, K, NST><<<grid, block, smem, st>>>(m, a);
   return cudaGetLastError();
 }
@@ -397,12 +399,9 @@ cudaError_t launch_sliced(const CUtensorMap& m, const TileArgs& a, uint32_t grid
 template <class A, int K, int NST, int SS>
 cudaError_t launch_assist(const CUtensorMap& m, const TileArgs& a, uint32_t grid, uint32_t, size_t, cudaStream_t st) {
   constexpr int smem = Tiles<K, NST>::WARP_BYTES + SS * Assist<A>::WPB * 128 + 8 * NST;
-  static bool set = false;
-  if (!set) {
-    cudaError_t e = cudaFuncSetAttribute(digest_assist_kernel<A, K, NST, SS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return e;
-    set = true;
-  }
+  static bool done[64] = {};
+  cudaError_t e0 = allow_smem(digest_assist_kernel<A, K, NST, SS>, done, smem);
+  if (e0 != cudaSuccess) return e0;
   digest_assist_kernel<A, K, NST, SS><<<grid, 64, smem, st>>>(m, a);
   return cudaGetLastError();
 }

@@ -1,0 +1,65 @@
+'use strict'
+/**
+ * Batched digest front end over the N-API add-on (js/addon).  WRITTEN, NOT EXECUTED on this image.
+ *
+ * Keeps the call shapes the reference's dependencies use, but batched and asynchronous:
+ *   simple-sha1:   sha1(buf, cb) / sha1.sync(buf)             -> sha1Batch(slot, msgs, expected?)
+ *   minio-js:      getHashSummer(enableSHA256) -> {md5sum: base64, sha256sum: hex}
+ *                                                             -> partDigests(slot, parts, {enableSHA256})
+ */
+const addon = require('../addon/build/Release/tritonhash.node')
+
+const SHA1 = addon.SHA1
+const MD5 = addon.MD5
+const SHA256 = addon.SHA256
+
+let started = false
+
+function init (gpuIds = [0], ringBytesPerGpu = 1 << 30) {
+  if (!started) {
+    addon.init(gpuIds, ringBytesPerGpu) // throws when no sm_100 GPU: there is no CPU fallback
+    started = true
+  }
+}
+
+function shutdown () {
+  if (started) addon.shutdown()
+  started = false
+}
+
+/** pinned slot the caller fills, e.g. `await fd.read(buffer, 0, n, pos)` */
+function ringAcquire (gpu, bytes) {
+  return addon.ringAcquire(gpu, bytes)
+}
+
+/**
+ * SHA-1 of every message of a slot; with `expected` (n x 20 raw bytes, info.pieces) also the verified
+ * bitfield: bit i <=> webtorrent's `hash === this._hashes[i]`.
+ * @returns {Promise<{hex: string[], ok: boolean[]|null}>}
+ */
+async function sha1Batch (slot, msgs, expected) {
+  const r = await addon.hashBatch(SHA1, slot, msgs, expected)
+  const hex = msgs.map((_, i) => r.sha1.toString('hex', i * 20, i * 20 + 20)) // lower-case hex, as simple-sha1
+  let ok = null
+  if (r.okBits) ok = msgs.map((_, i) => ((r.okBits.readUInt32LE((i >>> 5) * 4) >>> (i & 31)) & 1) === 1)
+  return { hex, ok, raw: r.sha1 }
+}
+
+/** getHashSummer for all parts at once: [{md5sum: base64 | '', sha256sum: hex | ''}] plus the raw md5s */
+async function partDigests (slot, parts, { enableSHA256 = false, both = false } = {}) {
+  const algs = both ? (MD5 | SHA256) : (enableSHA256 ? SHA256 : MD5)
+  const r = await addon.hashBatch(algs, slot, parts)
+  const out = parts.map((_, i) => ({
+    md5sum: r.md5 ? r.md5.toString('base64', i * 16, i * 16 + 16) : '',
+    sha256sum: r.sha256 ? r.sha256.toString('hex', i * 32, i * 32 + 32) : ''
+  }))
+  return { digests: out, md5: r.md5 || null, sha256: r.sha256 || null }
+}
+
+/** S3 multipart ETag of one object from its raw part md5s: hex(md5(concat)) + '-' + N */
+function multipartEtag (md5s) {
+  const n = md5s.length / 16
+  return addon.etagCombine(md5s, [n]).toString('hex') + '-' + n
+}
+
+module.exports = { SHA1, MD5, SHA256, init, shutdown, ringAcquire, sha1Batch, partDigests, multipartEtag, stats: () => addon.stats() }

@@ -232,3 +232,59 @@ def test_stage_chain_download_process_upload(eng, tmp_path):
     assert keys == sorted(["j9/original/" + base64.b64encode(b"e1.mkv").decode(), "j9/original/done"])
     e1 = (seed / "Show" / "Season 1" / "e1.mkv").read_bytes()
     assert mock.statObject("triton-staging", keys[0] if keys[0].endswith("done") is False else keys[1])["etag"] == hashlib.md5(e1).hexdigest()
+
+
+def test_config4_shape_scaled_mixed_pieces_and_parts_from_pinned_ring(eng, tmp_path):
+    """BASELINE config 4 scaled down: media files hashed twice from the pinned ring — as torrent pieces
+    (1/2/4 MiB, SHA-1 + bitfield) and as S3 parts (8/16/32/64 MiB, MD5 + SHA-256) — with short last piece /
+    part; every digest against libcrypto."""
+    from downloader_b200 import s3 as s3f
+    from downloader_b200.reader import hash_file_parts, piece_bounds, verify_pieces
+    rng = np.random.default_rng(40)
+    sizes = [int(rng.integers(70, 140)) * MiB + int(rng.integers(1, MiB)) for _ in range(3)]
+    for k, size in enumerate(sizes):
+        path = str(tmp_path / f"media{k}.mkv")
+        data = make_file(path, 500 + k, size)
+        plen = [1, 2, 4][k % 3] * MiB
+        psize = [8, 16, 32, 64][(k + 1) % 4] * MiB
+        pb = piece_bounds(size, plen)
+        off = np.array([s for s, _ in pb], np.uint64)
+        ln = np.array([e - s for s, e in pb], np.uint64)
+        _, exp = oracle.evp_batch(oracle.SHA1, data, off, ln, threads=16)
+        bad = [0, len(pb) - 1]
+        table = exp[oracle.SHA1].copy()
+        for b in bad:
+            table[b, 0] ^= 0x55
+        res = verify_pieces(eng, [(path, size)], plen, table, batch_bytes=48 * MiB, in_flight=3)
+        assert (res[1] == exp[oracle.SHA1]).all()
+        assert np.nonzero(~res["ok"])[0].tolist() == bad
+        ranges = s3f.part_ranges(size, psize)
+        d = hash_file_parts(eng, path, ranges, batch_bytes=150 * MiB)
+        off = np.array([s for s, _ in ranges], np.uint64)
+        ln = np.array([e - s for s, e in ranges], np.uint64)
+        _, exp = oracle.evp_batch(oracle.MD5 | oracle.SHA256, data, off, ln, threads=16, chunk=65536)
+        assert (d[2] == exp[oracle.MD5]).all() and (d[4] == exp[oracle.SHA256]).all()
+        assert s3f.multipart_etag(eng, d[2])[0] == oracle.etag_multipart(exp[oracle.MD5])
+
+
+def test_one_context_drives_two_gpus(tmp_path):
+    """th_init with a GPU list: per-GPU rings/streams in one process, pieces sharded by index."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run under gpurun --gpus 2)")
+    from downloader_b200 import Engine
+    from downloader_b200.sharding import shard_range
+    n, ln = 64, 65536
+    data = oracle.synth_batch(0, n, ln)
+    exp = oracle.batch(oracle.SHA1, data, np.arange(n, dtype=np.uint64) * ln, np.full(n, ln, np.uint64), threads=8)
+    with Engine([0, 1], ring_bytes=8 * MiB) as e2:
+        tickets = []
+        for g in (0, 1):
+            lo, hi = shard_range(n, 2, g)
+            slot, view = e2.ring_acquire((hi - lo) * ln, gpu=g)
+            view[:] = data[lo * ln:hi * ln]
+            tickets.append((lo, hi, e2.submit(slot, np.arange(hi - lo, dtype=np.uint64) * ln, np.full(hi - lo, ln, np.uint64), 1, exp[lo:hi])))
+        for lo, hi, t in tickets:
+            r = e2.result(t, hi - lo, 1, want_ok=True)
+            assert (r[1] == exp[lo:hi]).all() and r["ok"].all()
+        assert e2.stats(0)["submits"] == 1 and e2.stats(1)["submits"] == 1 and e2.stats()["submits"] == 2
