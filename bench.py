@@ -31,6 +31,8 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# kernels of different submits run on different streams; give them distinct hardware queues (read at context creation)
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 
 GB = 1e9
 SM_COUNT = 148
@@ -184,6 +186,7 @@ def main():
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--e2e-slots", type=int, default=8)
+    ap.add_argument("--e2e-gib", type=int, default=16, help="cap on the pinned bytes the e2e leg cycles through per GPU")
     ap.add_argument("--staging", default="", help="override bulk staging geometry, e.g. 512x2 (tuning only)")
     ap.add_argument("--path", type=int, default=0, help="0 auto, 1 bulk, 2 tile, 3 sliced (tuning only)")
     args = ap.parse_args()
@@ -297,6 +300,7 @@ def main():
         # pinned-memory budget: never ask for more than ~45 % of the host's available RAM over all ranks
         avail = _mem_available()
         budget = int(0.45 * avail / world) if avail else total_bytes
+        budget = min(budget, args.e2e_gib << 30)
         while per_slot > 32 and slots * per_slot * ln > budget:
             per_slot //= 2
         slot_bytes = per_slot * ln

@@ -12,6 +12,7 @@
 #include <algorithm>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <deque>
 #include <mutex>
@@ -76,9 +77,22 @@ struct Ticket {
   struct th_ctx* ctx = nullptr;
 };
 
+// Kernels of different submits must be able to overlap: a slot of large parts holds only a few message
+// groups, and a chain's latency (0.26 s for a 16 MiB SHA-256 part) is far longer than the slot's H2D copy.
+// Tickets therefore rotate over a pool of stream sets; only the H2D copies share one stream (one PCIe link).
+constexpr int kStreamSets = 8;
+// 8 sets x 3 digest streams + copy + misc = 26 streams: below the 32 hardware work queues a process can ask
+// for (CUDA_DEVICE_MAX_CONNECTIONS, set in th_init when CUDA is not initialised yet).  With the default of 8
+// queues streams alias, and a D2H copy queued behind a 0.26 s kernel stalls unrelated kernels in its queue.
+struct StreamSet {
+  cudaStream_t alg[3] = {nullptr, nullptr, nullptr};
+};
+
 struct Gpu {
   int dev = -1;
-  cudaStream_t s_copy = nullptr, s_alg[3] = {nullptr, nullptr, nullptr}, s_done = nullptr;
+  cudaStream_t s_copy = nullptr, s_misc = nullptr;  // H2D copies; synchronous odd jobs (ETag combine)
+  StreamSet sets[kStreamSets];
+  uint64_t next_set = 0;
   uint8_t* ring_h = nullptr;
   uint8_t* ring_d = nullptr;
   size_t ring_bytes = 0;
@@ -216,10 +230,13 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, size_t copy_off
   const size_t dlen[3] = {20, 16, 32};
   const size_t ok_bytes = ((n + 31) / 32) * 4;
   const uint8_t* d_uni = d_base + msgs[0].offset;
+  StreamSet& ss = g.sets[g.next_set++ % kStreamSets];
+  int primary = -1;
+  std::vector<cudaEvent_t> joins;
 
   for (int a = 0; a < 3; a++) {
     if (!(mask & (1u << a))) continue;
-    cudaStream_t st = g.s_alg[a];
+    cudaStream_t st = ss.alg[a];
     CU(c, cudaStreamWaitEvent(st, ev_in, 0));
     int rc = TH_OK;
     CU(c, cudaEventCreate(&t->ev_k0[a]));
@@ -260,18 +277,26 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, size_t copy_off
       CU(c, cudaMemcpyAsync(jb->h + jb->o_ok(n), jb->d + jb->o_ok(n), ok_bytes, cudaMemcpyDeviceToHost, st));
       g.st.d2h_bytes += ok_bytes;
     }
-    cudaEvent_t ev_a;
-    CU(c, cudaEventCreateWithFlags(&ev_a, cudaEventDisableTiming));
-    CU(c, cudaEventRecord(ev_a, st));
-    CU(c, cudaStreamWaitEvent(g.s_done, ev_a, 0));
-    CU(c, cudaEventDestroy(ev_a));
+    if (primary < 0) {
+      primary = a;  // the first requested digest's stream also carries the ticket's completion
+    } else {
+      cudaEvent_t ev_a;
+      CU(c, cudaEventCreateWithFlags(&ev_a, cudaEventDisableTiming));
+      CU(c, cudaEventRecord(ev_a, st));
+      joins.push_back(ev_a);
+    }
   }
   CU(c, cudaEventDestroy(ev_in));
+  cudaStream_t sp = ss.alg[primary];
+  for (cudaEvent_t ev : joins) {
+    CU(c, cudaStreamWaitEvent(sp, ev, 0));
+    CU(c, cudaEventDestroy(ev));
+  }
   // the callback is enqueued before ev_done so that a ticket cannot be retired (th_result waits on
   // ev_done) while its callback is still pending
-  if (t->cb) CU(c, cudaLaunchHostFunc(g.s_done, host_done, t));
+  if (t->cb) CU(c, cudaLaunchHostFunc(sp, host_done, t));
   CU(c, cudaEventCreateWithFlags(&t->ev_done, cudaEventDisableTiming));
-  CU(c, cudaEventRecord(t->ev_done, g.s_done));
+  CU(c, cudaEventRecord(t->ev_done, sp));
   g.st.bytes += total;
   g.st.submits += 1;
   return TH_OK;
@@ -304,6 +329,7 @@ extern "C" {
 int th_init(const int* gpu_ids, int n_gpus, size_t ring_bytes_per_gpu, th_ctx** out) {
   if (!out || n_gpus <= 0) return TH_EINVAL;
   *out = nullptr;
+  setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);  // read when the CUDA context is created; no effect if it already exists
   int count = 0;
   if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return TH_ENODEVICE;
   th_ctx* c = new th_ctx();
@@ -318,8 +344,9 @@ int th_init(const int* gpu_ids, int n_gpus, size_t ring_bytes_per_gpu, th_ctx** 
     }
     cudaError_t e = cudaSetDevice(g.dev);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&g.s_copy, cudaStreamNonBlocking);
-    for (int a = 0; a < 3 && e == cudaSuccess; a++) e = cudaStreamCreateWithFlags(&g.s_alg[a], cudaStreamNonBlocking);
-    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&g.s_done, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&g.s_misc, cudaStreamNonBlocking);
+    for (int k = 0; k < kStreamSets && e == cudaSuccess; k++)
+      for (int a = 0; a < 3 && e == cudaSuccess; a++) e = cudaStreamCreateWithFlags(&g.sets[k].alg[a], cudaStreamNonBlocking);
     if (e == cudaSuccess && ring_bytes_per_gpu) {
       g.ring_bytes = align_up(ring_bytes_per_gpu, kRingAlign);
       e = cudaHostAlloc((void**)&g.ring_h, g.ring_bytes, cudaHostAllocPortable);
@@ -345,8 +372,9 @@ int th_shutdown(th_ctx* c) {
     if (g.ring_h) cudaFreeHost(g.ring_h);
     if (g.ring_d) cudaFree(g.ring_d);
     if (g.s_copy) cudaStreamDestroy(g.s_copy);
-    for (auto& s : g.s_alg) if (s) cudaStreamDestroy(s);
-    if (g.s_done) cudaStreamDestroy(g.s_done);
+    if (g.s_misc) cudaStreamDestroy(g.s_misc);
+    for (auto& ss : g.sets)
+      for (auto& s : ss.alg) if (s) cudaStreamDestroy(s);
   }
   for (auto& kv : c->tickets) {
     Ticket* t = kv.second;
@@ -546,7 +574,7 @@ int th_etag_combine(th_ctx* c, int gpu, const uint8_t* md5s, const uint32_t* cou
   const size_t b_md5 = align_up(parts * 16 + 16, 256), b_pre = align_up((n_objects + 1) * 8, 256), b_out = n_objects * 16;
   uint8_t* d = nullptr;
   CU(c, cudaMalloc((void**)&d, b_md5 + b_pre + b_out));
-  cudaStream_t st = g.s_alg[1];
+  cudaStream_t st = g.s_misc;
   cudaError_t e = cudaSuccess;
   if (parts) e = cudaMemcpyAsync(d, md5s, parts * 16, cudaMemcpyHostToDevice, st);
   if (e == cudaSuccess) e = cudaMemcpyAsync(d + b_md5, prefix.data(), (n_objects + 1) * 8, cudaMemcpyHostToDevice, st);

@@ -399,3 +399,34 @@ def test_config2_full_size_properties(torch, L):
         assert (host[j * ln:(j + 1) * ln] == oracle.synth(i, ln)).all()
     _, e = oracle.evp_batch(SHA1, host, (np.arange(len(pick)) * ln).astype(np.uint64), np.full(len(pick), ln, np.uint64), threads=16)
     assert (digs[pick] == e[SHA1]).all()
+
+
+def test_messages_longer_than_512_mib_and_2_gib(torch, L):
+    """64-bit length handling: the bit-length field needs its high word from 512 MiB up (tensor-map kernels),
+    and from 2 GiB up a message leaves the tensor-map path (per-lane bulk copies, 64-bit byte offsets)."""
+    free, _ = torch.cuda.mem_get_info()
+    if free < (6 << 30):
+        pytest.skip("not enough free HBM")
+    ln = (1 << 29) + 64 + 1
+    n = 2
+    stride = (ln + 15) & ~15
+    d = torch.empty(n * stride, dtype=torch.uint8, device="cuda")
+    assert L.th_synth_fill(d.data_ptr(), 0, n, ln, stride, 77, None) == 0
+    outs = {a: torch.zeros(n * oracle.DIGEST_LEN[a], dtype=torch.uint8, device="cuda") for a in (SHA1, MD5, SHA256)}
+    assert L.th_sha1_batch(d.data_ptr(), None, None, None, stride, ln, n, outs[SHA1].data_ptr(), None, None, None) == 0
+    assert L.th_md5_batch(d.data_ptr(), None, None, None, stride, ln, n, outs[MD5].data_ptr(), None) == 0
+    assert L.th_sha256_batch(d.data_ptr(), None, None, None, stride, ln, n, outs[SHA256].data_ptr(), None) == 0
+    torch.cuda.synchronize()
+    host = d.cpu().numpy()
+    for a in (SHA1, MD5, SHA256):
+        got = outs[a].cpu().numpy().reshape(n, -1)
+        for i in range(n):
+            assert got[i].tobytes() == hashlib.new(NAMES[a], host[i * stride:i * stride + ln]).digest(), (NAMES[a], i)
+    del d, host
+    ln = (1 << 31) + 16 + 5   # beyond the tensor map's 2^31 coordinate range
+    d = torch.empty(ln, dtype=torch.uint8, device="cuda")
+    assert L.th_synth_fill(d.data_ptr(), 3, 1, ln, ln, 78, None) == 0
+    o = torch.zeros(16, dtype=torch.uint8, device="cuda")
+    assert L.th_md5_batch(d.data_ptr(), None, None, None, ln, ln, 1, o.data_ptr(), None) == 0
+    torch.cuda.synchronize()
+    assert o.cpu().numpy().tobytes() == hashlib.md5(d.cpu().numpy()).digest()
