@@ -54,9 +54,11 @@ struct Slot {
   uint64_t id = 0;
   int gpu = 0;
   size_t off = 0, bytes = 0;   // region of the ring
+  size_t used = 0;             // bytes the caller asked for (what the H2D copy moves)
   bool submitted = false;
-  bool done = false;           // ticket completed (or released) -> region reusable
-  uint64_t ticket = 0;
+  bool done = false;           // every ticket completed (or slot released) -> region reusable
+  std::vector<uint64_t> tickets;  // a slot may be submitted several times (pieces AND parts of the same bytes)
+  cudaEvent_t ev_copied = nullptr;  // H2D of the slot, issued by its first submit
 };
 
 struct Ticket {
@@ -152,18 +154,23 @@ JobBuf* get_job(th_ctx* c, Gpu& g, size_t n, int* rc) {
 void reap(th_ctx* c, Gpu& g, bool block_on_oldest) {
   for (auto& s : g.slots) {
     if (s.done || !s.submitted) continue;
-    auto it = c->tickets.find(s.ticket);
-    if (it == c->tickets.end()) { s.done = true; continue; }
-    Ticket* t = it->second;
-    if (!t->finished) {
-      cudaError_t e = (block_on_oldest && &s == &g.slots.front()) ? cudaEventSynchronize(t->ev_done)
-                                                                  : cudaEventQuery(t->ev_done);
-      if (e == cudaSuccess) t->finished = true;
-      else if (e != cudaErrorNotReady) { t->finished = true; t->status = cuda_fail(c, e, "ticket event"); }
+    bool all = true;
+    for (uint64_t id : s.tickets) {
+      auto it = c->tickets.find(id);
+      if (it == c->tickets.end()) continue;  // already retired by th_result
+      Ticket* t = it->second;
+      if (!t->finished) {
+        cudaError_t e = (block_on_oldest && &s == &g.slots.front()) ? cudaEventSynchronize(t->ev_done)
+                                                                    : cudaEventQuery(t->ev_done);
+        if (e == cudaSuccess) t->finished = true;
+        else if (e != cudaErrorNotReady) { t->finished = true; t->status = cuda_fail(c, e, "ticket event"); }
+      }
+      all &= t->finished;
     }
-    if (t->finished) s.done = true;
+    if (all) s.done = true;
   }
   while (!g.slots.empty() && g.slots.front().done) {
+    if (g.slots.front().ev_copied) cudaEventDestroy(g.slots.front().ev_copied);
     g.slots.pop_front();
     g.head = g.slots.empty() ? g.tail : g.slots.front().off;
   }
@@ -175,8 +182,8 @@ void CUDART_CB host_done(void* p) {
   if (t->cb) t->cb(t->user, t->id, TH_OK);
 }
 
-int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, size_t copy_off, size_t copy_bytes,
-            const th_msg* msgs, size_t n, uint32_t mask, const uint8_t* expected) {
+int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, const th_msg* msgs, size_t n,
+            uint32_t mask, const uint8_t* expected) {
   JobBuf* jb = t->jb;
   uint64_t* h_off = reinterpret_cast<uint64_t*>(jb->h + jb->o_off(n));
   uint64_t* h_len = reinterpret_cast<uint64_t*>(jb->h + jb->o_len(n));
@@ -210,10 +217,12 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, size_t copy_off
   if (expected) std::memcpy(jb->h + jb->o_exp(n), expected, n * 20);
 
   CU(c, cudaSetDevice(g.dev));
-  // H2D: payload (ring slot) then descriptors, one copy each.
-  if (copy_bytes) {
-    CU(c, cudaMemcpyAsync(g.ring_d + copy_off, g.ring_h + copy_off, copy_bytes, cudaMemcpyHostToDevice, g.s_copy));
-    g.st.h2d_bytes += copy_bytes;
+  // H2D: payload (the whole ring slot, once — later submits on the same slot reuse it) then descriptors.
+  if (slot && !slot->ev_copied) {
+    CU(c, cudaMemcpyAsync(g.ring_d + slot->off, g.ring_h + slot->off, slot->used, cudaMemcpyHostToDevice, g.s_copy));
+    g.st.h2d_bytes += slot->used;
+    CU(c, cudaEventCreateWithFlags(&slot->ev_copied, cudaEventDisableTiming));
+    CU(c, cudaEventRecord(slot->ev_copied, g.s_copy));
   }
   const size_t desc_bytes = expected ? jb->o_sha1(n) : (use_order ? jb->o_exp(n) : jb->o_ord(n));
   CU(c, cudaMemcpyAsync(jb->d, jb->h, desc_bytes, cudaMemcpyHostToDevice, g.s_copy));
@@ -413,6 +422,7 @@ int th_ring_acquire(th_ctx* c, int gpu, size_t bytes, void** host_ptr, th_slot* 
       s.gpu = gpu;
       s.off = off;
       s.bytes = need;
+      s.used = (bytes + 15) & ~(size_t)15;
       if (g.slots.empty()) g.head = off;
       g.tail = off + need;
       g.slots.push_back(s);
@@ -459,20 +469,15 @@ static int submit_common(th_ctx* c, int gpu, Slot* slot, const void* d_base_user
   t->user = user;
   t->ctx = c;
   const uint8_t* d_base = slot ? g.ring_d + slot->off : static_cast<const uint8_t*>(d_base_user);
-  size_t used = 0;
-  if (slot) {
-    for (size_t i = 0; i < n; i++) used = std::max<size_t>(used, (size_t)(msgs[i].offset + msgs[i].length));
-    used = align_up(used, 16);
-    t->slot_id = slot->id;
-  }
-  rc = enqueue(c, g, t, d_base, slot ? slot->off : 0, used, msgs, n, mask, t->has_expected ? expected : nullptr);
+  if (slot) t->slot_id = slot->id;
+  rc = enqueue(c, g, t, d_base, slot, msgs, n, mask, t->has_expected ? expected : nullptr);
   if (rc != TH_OK) {
     free_ticket_events(t);
     g.free_jobs.push_back(jb);
     delete t;
     return rc;
   }
-  if (slot) { slot->submitted = true; slot->ticket = t->id; }
+  if (slot) { slot->submitted = true; slot->tickets.push_back(t->id); }
   c->tickets[t->id] = t;
   *out = t->id;
   return TH_OK;
@@ -486,8 +491,8 @@ int th_submit(th_ctx* c, th_slot slot_id, const th_msg* msgs, size_t n, uint32_t
   for (size_t gi = 0; gi < c->gpus.size(); gi++)
     for (auto& s : c->gpus[gi].slots)
       if (s.id == slot_id) {
-        if (s.submitted || s.done) return TH_ESTATE;
-        int rc = validate(msgs, n, mask, s.bytes);
+        if (s.done) return TH_ESTATE;
+        int rc = validate(msgs, n, mask, s.used);
         if (rc != TH_OK) return rc;
         return submit_common(c, (int)gi, &s, nullptr, msgs, n, mask, expected, cb, user, out);
       }
@@ -548,9 +553,6 @@ int th_result(th_ctx* c, th_ticket id, uint8_t* sha1, uint8_t* md5, uint8_t* sha
     if (ok_bits) { if (!t->has_expected) rc = TH_EINVAL; else std::memcpy(ok_bits, jb->h + jb->o_ok(n), ((n + 31) / 32) * 4); }
   }
   Gpu& g = c->gpus[(size_t)t->gpu];
-  if (t->slot_id)
-    for (auto& s : g.slots)
-      if (s.id == t->slot_id) s.done = true;
   free_ticket_events(t);
   g.free_jobs.push_back(jb);
   c->tickets.erase(it);

@@ -144,3 +144,60 @@ def verify_pieces(engine, files: Sequence[Tuple[str, int]], piece_length: int, e
         return _stream_messages(engine, src, bounds, ALG_SHA1, exp, gpu, batch_bytes, in_flight)
     finally:
         src.close()
+
+
+def hash_media_file(engine, path: str, piece_length: int, expected_sha1, part_ranges: Sequence[Tuple[int, int]],
+                    part_algs: int = ALG_MD5 | ALG_SHA256, gpu: int = 0, batch_bytes: int = 512 << 20, in_flight: int = 2) -> dict:
+    """One pass over a staged media file feeding BOTH consumers of its bytes: SHA-1 by torrent piece (with
+    the fused verify) and MD5 / SHA-256 by S3 part.  Each ring slot is read once, crosses PCIe once, and is
+    submitted twice (th_submit allows that).  Slots hold whole parts, and parts are multiples of the piece
+    length, so both message lists tile every slot.  Returns {'pieces': {...}, 'parts': {...}}."""
+    size = os.path.getsize(path)
+    part_ranges = list(part_ranges)
+    pb = piece_bounds(size, piece_length)
+    exp = None if expected_sha1 is None else np.ascontiguousarray(expected_sha1, np.uint8).reshape(-1, 20)
+    pieces = {ALG_SHA1: np.zeros((len(pb), 20), np.uint8)}
+    if exp is not None:
+        pieces["ok"] = np.zeros(len(pb), bool)
+    parts = {a: np.zeros((len(part_ranges), DIGEST_LEN[a]), np.uint8) for a in (ALG_MD5, ALG_SHA256) if part_algs & a}
+    src = _ConcatFiles([(path, size)])
+    pending: List[tuple] = []
+
+    def drain(k):
+        while len(pending) > k:
+            tp, p0, pn, tq, q0, qn = pending.pop(0)
+            r = engine.result(tp, pn, ALG_SHA1, want_ok=exp is not None)
+            pieces[ALG_SHA1][p0:p0 + pn] = r[ALG_SHA1]
+            if exp is not None:
+                pieces["ok"][p0:p0 + pn] = r["ok"]
+            r = engine.result(tq, qn, part_algs)
+            for a in parts:
+                parts[a][q0:q0 + qn] = r[a]
+
+    try:
+        q = 0
+        while q < len(part_ranges):
+            start = part_ranges[q][0]
+            q1 = q
+            while q1 < len(part_ranges) and part_ranges[q1][1] - start <= batch_bytes:
+                q1 += 1
+            q1 = max(q1, q + 1)
+            end = part_ranges[q1 - 1][1]
+            if start % piece_length:
+                raise ValueError("part boundaries must be multiples of the piece length")
+            drain(in_flight - 1)
+            slot, view = engine.ring_acquire(max(end - start, 16), gpu)
+            src.readinto(view[:end - start], start)
+            p0, p1 = start // piece_length, -(-end // piece_length)
+            offs = np.array([pb[i][0] - start for i in range(p0, p1)], np.uint64)
+            lens = np.array([pb[i][1] - pb[i][0] for i in range(p0, p1)], np.uint64)
+            tp = engine.submit(slot, offs, lens, ALG_SHA1, exp[p0:p1] if exp is not None else None)
+            offs = np.array([part_ranges[i][0] - start for i in range(q, q1)], np.uint64)
+            lens = np.array([part_ranges[i][1] - part_ranges[i][0] for i in range(q, q1)], np.uint64)
+            tq = engine.submit(slot, offs, lens, part_algs)   # same slot, second message list: no second copy
+            pending.append((tp, p0, p1 - p0, tq, q, q1 - q))
+            q = q1
+        drain(0)
+    finally:
+        src.close()
+    return {"pieces": pieces, "parts": parts}

@@ -85,6 +85,9 @@ int th_ring_acquire(th_ctx* ctx, int gpu, size_t bytes, void** host_ptr, th_slot
 int th_ring_release(th_ctx* ctx, th_slot slot);
 
 /* Non-blocking.  Hashes msgs[0..n) of the slot with every digest in alg_mask.
+ * A slot may be submitted more than once while one of its tickets is still outstanding — e.g. once as
+ * torrent pieces (SHA-1) and once as S3 parts (MD5 | SHA-256) of the same bytes: the slot crosses PCIe
+ * once, with its first submit, and returns to the ring when all of its tickets have completed.
  * expected_sha1 (nullable, n*20 raw bytes = info.pieces of the .torrent, [dep] parse-torrent@7.0.0)
  * enables the fused compare: bit i of ok_bits = (sha1(msg i) == expected i), which is webtorrent's
  * `hash === this._hashes[index]` -> bitfield.set(index) ([dep] lib/torrent.js). */

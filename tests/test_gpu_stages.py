@@ -267,6 +267,32 @@ def test_config4_shape_scaled_mixed_pieces_and_parts_from_pinned_ring(eng, tmp_p
         assert s3f.multipart_etag(eng, d[2])[0] == oracle.etag_multipart(exp[oracle.MD5])
 
 
+def test_one_pass_feeds_pieces_and_parts_from_the_same_slot(eng, tmp_path):
+    """the same bytes hashed as torrent pieces and as S3 parts with one H2D copy per slot."""
+    from downloader_b200 import s3 as s3f
+    from downloader_b200.reader import hash_media_file, piece_bounds
+    size = 150 * MiB + 4321
+    path = str(tmp_path / "m.mkv")
+    data = make_file(path, 900, size)
+    plen, psize = 2 * MiB, 16 * MiB
+    pb = piece_bounds(size, plen)
+    _, e1 = oracle.evp_batch(oracle.SHA1, data, np.array([s for s, _ in pb], np.uint64), np.array([e - s for s, e in pb], np.uint64), threads=16)
+    table = e1[oracle.SHA1].copy()
+    table[7, 1] ^= 1
+    ranges = s3f.part_ranges(size, psize)
+    s0 = eng.stats()
+    r = hash_media_file(eng, path, plen, table, ranges, batch_bytes=64 * MiB, in_flight=2)
+    s1 = eng.stats()
+    assert (r["pieces"][1] == e1[oracle.SHA1]).all()
+    assert np.nonzero(~r["pieces"]["ok"])[0].tolist() == [7]
+    _, e2 = oracle.evp_batch(oracle.MD5 | oracle.SHA256, data, np.array([s for s, _ in ranges], np.uint64),
+                             np.array([e - s for s, e in ranges], np.uint64), threads=16, chunk=65536)
+    assert (r["parts"][2] == e2[oracle.MD5]).all() and (r["parts"][4] == e2[oracle.SHA256]).all()
+    payload = s1["h2d_bytes"] - s0["h2d_bytes"]
+    assert size <= payload < size + 4 * MiB, "the slot must cross PCIe once, not once per submit"
+    assert s1["submits"] - s0["submits"] == 2 * 3 and s1["bytes"] - s0["bytes"] == 2 * size
+
+
 def test_one_context_drives_two_gpus(tmp_path):
     """th_init with a GPU list: per-GPU rings/streams in one process, pieces sharded by index."""
     import torch
