@@ -82,8 +82,8 @@ struct Ticket {
 // Kernels of different submits must be able to overlap: a slot of large parts holds only a few message
 // groups, and a chain's latency (0.26 s for a 16 MiB SHA-256 part) is far longer than the slot's H2D copy.
 // Tickets therefore rotate over a pool of stream sets; only the H2D copies share one stream (one PCIe link).
-constexpr int kStreamSets = 8;
-// 8 sets x 3 digest streams + copy + misc = 26 streams: below the 32 hardware work queues a process can ask
+constexpr int kStreamSets = 10;
+// 10 sets x 3 digest streams + copy + misc = 32 streams: exactly the 32 hardware work queues a process can ask
 // for (CUDA_DEVICE_MAX_CONNECTIONS, set in th_init when CUDA is not initialised yet).  With the default of 8
 // queues streams alias, and a D2H copy queued behind a 0.26 s kernel stalls unrelated kernels in its queue.
 struct StreamSet {
@@ -94,7 +94,7 @@ struct Gpu {
   int dev = -1;
   cudaStream_t s_copy = nullptr, s_misc = nullptr;  // H2D copies; synchronous odd jobs (ETag combine)
   StreamSet sets[kStreamSets];
-  uint64_t next_set = 0;
+  uint64_t next_stream[3] = {0, 0, 0};  // each digest rotates over its own 10 streams, whatever mix of submits arrives
   uint8_t* ring_h = nullptr;
   uint8_t* ring_d = nullptr;
   size_t ring_bytes = 0;
@@ -239,13 +239,14 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
   const size_t dlen[3] = {20, 16, 32};
   const size_t ok_bytes = ((n + 31) / 32) * 4;
   const uint8_t* d_uni = d_base + msgs[0].offset;
-  StreamSet& ss = g.sets[g.next_set++ % kStreamSets];
+  cudaStream_t tstream[3] = {nullptr, nullptr, nullptr};
   int primary = -1;
   std::vector<cudaEvent_t> joins;
 
   for (int a = 0; a < 3; a++) {
     if (!(mask & (1u << a))) continue;
-    cudaStream_t st = ss.alg[a];
+    cudaStream_t st = g.sets[g.next_stream[a]++ % kStreamSets].alg[a];
+    tstream[a] = st;
     CU(c, cudaStreamWaitEvent(st, ev_in, 0));
     int rc = TH_OK;
     CU(c, cudaEventCreate(&t->ev_k0[a]));
@@ -296,7 +297,7 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
     }
   }
   CU(c, cudaEventDestroy(ev_in));
-  cudaStream_t sp = ss.alg[primary];
+  cudaStream_t sp = tstream[primary];
   for (cudaEvent_t ev : joins) {
     CU(c, cudaStreamWaitEvent(sp, ev, 0));
     CU(c, cudaEventDestroy(ev));
