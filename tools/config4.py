@@ -65,11 +65,15 @@ def main():
     s0 = eng.stats()
     pending = []
 
+    prof = {"retire": 0.0, "acquire": 0.0, "submit": 0.0}
+
     def retire(k):
         while len(pending) > k:
             tp, np_, tq, nq, key = pending.pop(0)
+            t_ = time.perf_counter()
             rp = eng.result(tp, np_, ALG_SHA1)
             rq = eng.result(tq, nq, ALG_MD5 | ALG_SHA256)
+            prof["retire"] += time.perf_counter() - t_
             ref = first.setdefault(key, (rp, rq))
             assert (ref[0][ALG_SHA1] == rp[ALG_SHA1]).all() and (ref[1][ALG_SHA256] == rq[ALG_SHA256]).all()
             assert (ref[1][ALG_MD5] == rq[ALG_MD5]).all()
@@ -80,11 +84,15 @@ def main():
         while pos < size:
             nb = min(slot_bytes, size - pos)
             retire(n_slots - 1)
+            t_ = time.perf_counter()
             sid, _ = eng.ring_acquire(slot_bytes)  # full slot, so offsets stay slot-aligned and hold the window
+            prof["acquire"] += time.perf_counter() - t_
             po, pl = msgs(nb, plen)
             qo, ql = msgs(nb, psize)
+            t_ = time.perf_counter()
             tp = eng.submit(sid, po, pl, ALG_SHA1)
             tq = eng.submit(sid, qo, ql, ALG_MD5 | ALG_SHA256)
+            prof["submit"] += time.perf_counter() - t_
             pending.append((tp, po.size, tq, qo.size, (nb, plen, psize)))
             pos += nb
         per_file.append({"GiB": round(size / GiB, 2), "piece_MiB": plen // MiB, "part_MiB": psize // MiB})
@@ -105,7 +113,8 @@ def main():
                       "ring_GiB": a.ring_gib, "slot_MiB": a.slot_mib, "total_GiB": round(total / GiB, 1), "seconds": round(T, 2),
                       "e2e_GBps": round(total / T / 1e9, 2),
                       "h2d_GBps": round((s1["h2d_bytes"] - s0["h2d_bytes"]) / T / 1e9, 2),
-                      "launches": s1["launches"] - s0["launches"], "files": per_file}))
+                      "launches": s1["launches"] - s0["launches"], "kernel_ms_sum": round(s1["kernel_ms"] - s0["kernel_ms"], 1),
+                      "host_seconds": {k: round(v, 2) for k, v in prof.items()}, "files": per_file}))
     eng.close()
 
 
