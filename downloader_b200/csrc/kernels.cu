@@ -355,6 +355,8 @@ struct TileOpts {
   int rounds = 32;     // sliced kernel: target scheduling rounds (units per worker)
   int slice_min_groups = 12;  // sliced kernel: cut chains into segments when a CTA has more groups than this
   int sliced_min_groups = 592;  // auto: use the sliced kernel from this many 32-message groups
+  int tile_many_groups = 8192;  // auto: SHA-1 / SHA-256 batches with at least this many groups go back to one-warp CTAs
+                                // (many waves balance themselves and measured 1-12 % faster than the persistent kernel)
 };
 static TileOpts g_opts;
 
@@ -428,6 +430,7 @@ struct Plan {
   int path = 1;  // 1 bulk, 2 tile, 3 sliced
   int k = 0, nst = 0;
   uint32_t grid = 0, block = 32, workers = 0, segc = 0, nseg = 1, groups_per_cta = 0;
+  int variant = -1;  // index into g_tile_variants
   size_t smem = 0;
 };
 
@@ -442,7 +445,8 @@ static Plan make_plan(int ai, uint64_t stride, uint64_t len, uint32_t n) {
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  const bool sliced = g_opts.path == 3 || (g_opts.path == 0 && groups >= (uint32_t)g_opts.sliced_min_groups);
+  const bool many = ai != 1 && groups >= (uint32_t)g_opts.tile_many_groups;
+  const bool sliced = g_opts.path == 3 || (g_opts.path == 0 && groups >= (uint32_t)g_opts.sliced_min_groups && !many);
   if (sliced) {
     const TileVariant& v = g_tile_variants[g_sliced_selected[ai]];
     const uint32_t W = (uint32_t)g_opts.workers;
@@ -459,6 +463,7 @@ static Plan make_plan(int ai, uint64_t stride, uint64_t len, uint32_t n) {
     const size_t smem = sliced_smem(v.k, v.nst, W, Gmax, ns, S);
     if (smem <= 227 * 1024) {
       pl.path = 3; pl.k = v.k; pl.nst = v.nst; pl.grid = grid; pl.block = W * 32; pl.workers = W;
+      pl.variant = g_sliced_selected[ai];
       pl.segc = (nch + S - 1) / S; pl.nseg = (nch + pl.segc - 1) / pl.segc; pl.groups_per_cta = Gmax; pl.smem = smem;
       return pl;
     }
@@ -469,8 +474,8 @@ static Plan make_plan(int ai, uint64_t stride, uint64_t len, uint32_t n) {
     pl.smem = (size_t)2 * 2 * 4096 + 4 * (ai == 0 ? 80 : 64) * 128 + 16;
     return pl;
   }
-  const TileVariant& v = g_tile_variants[g_tile_selected[ai]];
-  pl.path = 2; pl.k = v.k; pl.nst = v.nst; pl.grid = groups; pl.block = 32;
+  const TileVariant& v = g_tile_variants[g_opts.path == 0 && many ? g_sliced_selected[ai] : g_tile_selected[ai]];
+  pl.path = 2; pl.k = v.k; pl.nst = v.nst; pl.grid = groups; pl.block = 32; pl.variant = int(&v - g_tile_variants);
   pl.smem = (size_t)v.k * v.nst * 4096 + 8 * v.nst;
   return pl;
 }
@@ -494,7 +499,7 @@ static int launch_uniform(int ai, const void* d_base, uint64_t stride, uint64_t 
     }
     return e == cudaSuccess ? TH_OK : TH_ECUDA;
   }
-  const TileVariant& v = g_tile_variants[pl.path == 3 ? g_sliced_selected[ai] : g_tile_selected[ai]];
+  const TileVariant& v = g_tile_variants[pl.variant];
   cudaError_t e = pl.path == 3 ? v.sliced[ai](tmap, a, pl.grid, pl.block, pl.smem, st)
                                : v.tile[ai](tmap, a, pl.grid, 32, 0, st);
   return e == cudaSuccess ? TH_OK : TH_ECUDA;
@@ -682,6 +687,7 @@ int th_set_option(const char* name, long long value) {
   if (k == "workers") { if (value < 4 || value > 16 || value % 4) return TH_EINVAL; th::g_opts.workers = (int)value; return TH_OK; }
   if (k == "slice_min_groups") { if (value < 0) return TH_EINVAL; th::g_opts.slice_min_groups = (int)value; return TH_OK; }
   if (k == "rounds") { if (value < 1 || value > 4096) return TH_EINVAL; th::g_opts.rounds = (int)value; return TH_OK; }
+  if (k == "tile_many_groups") { if (value < 1) return TH_EINVAL; th::g_opts.tile_many_groups = (int)value; return TH_OK; }
   if (k == "sliced_min_groups") { if (value < 1) return TH_EINVAL; th::g_opts.sliced_min_groups = (int)value; return TH_OK; }
   if (k == "tile_k" || k == "tile_stages") return TH_EINVAL;  // use th_set_tiling
   return TH_EINVAL;
