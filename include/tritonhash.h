@@ -185,7 +185,7 @@ int th_set_tiling(uint32_t alg, int tiles_per_stage, int stages);
 /* Tuning knobs (process-wide): "path" 0 auto | 1 per-lane bulk copies | 2 one-warp CTAs on tensor-map
  * tiles | 3 persistent time-sliced kernel | 4 chain + schedule-helper warp per group (SHA-1/SHA-256, few
  * large messages); "workers" 4|8|12|16 warps per SM for path 3; "rounds" scheduling rounds per worker for
- * path 3; "sliced_min_groups" / "assist_max_groups" auto thresholds (in 32-message groups). */
+ * path 3; "sliced_min_groups" / "assist_max_groups" / "tile_many_groups" auto thresholds (in 32-message groups). */
 int th_set_option(const char* name, long long value);
 /* Describes, as text, the kernel and geometry an equal-length batch of n messages would be run
  * with on the current device (what benchmarks record next to their numbers). */
