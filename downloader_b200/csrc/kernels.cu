@@ -445,7 +445,8 @@ static Plan make_plan(int ai, uint64_t stride, uint64_t len, uint32_t n) {
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  const bool many = ai != 1 && groups >= (uint32_t)g_opts.tile_many_groups;
+  // SHA-256 gains from one-warp CTAs from 8192 groups on (+4..12 %), SHA-1 only from twice that (+1 %)
+  const bool many = ai != 1 && groups >= (uint32_t)g_opts.tile_many_groups * (ai == 0 ? 2u : 1u);
   const bool sliced = g_opts.path == 3 || (g_opts.path == 0 && groups >= (uint32_t)g_opts.sliced_min_groups && !many);
   if (sliced) {
     const TileVariant& v = g_tile_variants[g_sliced_selected[ai]];
