@@ -75,6 +75,7 @@ def lib() -> C.CDLL:
     L.th_submit.argtypes = [vp, u64, C.POINTER(ThMsg), C.c_size_t, u32, vp, DONE_CB, vp, C.POINTER(u64)]
     L.th_submit_device.argtypes = [vp, i32, vp, C.POINTER(ThMsg), C.c_size_t, u32, vp, DONE_CB, vp, C.POINTER(u64)]
     L.th_wait.argtypes = [vp, u64]
+    L.th_ticket_timing.argtypes = [vp, u64, C.POINTER(C.c_double)]
     L.th_result.argtypes = [vp, u64, vp, vp, vp, vp]
     L.th_etag_combine.argtypes = [vp, i32, vp, vp, C.c_size_t, vp]
     L.th_stats_get.argtypes = [vp, i32, C.POINTER(ThStats)]

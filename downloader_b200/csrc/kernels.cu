@@ -8,6 +8,7 @@
 //                            completeMultipartUpload; lib/upload.js:45).
 //   synth_kernel             SURVEY §8d counter-based generator (benchmarks / tests).
 #include <cstdint>
+#include <atomic>
 #include <cstdio>
 #include <string>
 #include <cuda.h>  // CUtensorMap types only; the encoder is fetched with cudaGetDriverEntryPoint (no -lcuda)
@@ -75,7 +76,24 @@ struct TileArgs {
   const uint8_t* expected;  // SHA-1 only, nullable
   uint32_t* ok_bits;        // SHA-1 only, nullable
   uint32_t one;             // the value 1, opaque to the compiler (see add_fma)
+  uint32_t salt;            // small grids: CTA b works on group (b + gridDim.x - salt) % gridDim.x, see spread_group
 };
+
+// A kernel with only a few CTAs always gets the same first SMs, so several such kernels running at once
+// (tickets of different ring slots, MD5 beside SHA-256) pile their long chains onto the same sub-partitions
+// while most of the chip idles: measured 1.05 s -> 1.45..1.9 s for eight concurrent 64 MiB-part submits.
+// Small grids are therefore padded to one CTA per SM and rotated by a per-launch salt; CTAs without a group
+// exit at once.  Returns false for such a CTA.
+__device__ __forceinline__ bool spread_group(const TileArgs& p, uint32_t* group) {
+  const uint32_t groups = (p.n + 31u) / 32u;
+  uint32_t g = blockIdx.x;
+  if (gridDim.x > groups) {
+    g = blockIdx.x + gridDim.x - p.salt;
+    if (g >= gridDim.x) g -= gridDim.x;
+  }
+  *group = g;
+  return g < groups;
+}
 
 template <class A>
 __device__ __forceinline__ void finish_group(const TileArgs& p, uint32_t group, int lane, const uint32_t* h) {
@@ -102,6 +120,8 @@ __global__ void __launch_bounds__(32) digest_tile_kernel(const __grid_constant__
   extern __shared__ __align__(1024) unsigned char smem[];
   using G = Tiles<K, NST>;
   const int lane = threadIdx.x;
+  uint32_t group;
+  if (!spread_group(p, &group)) return;
   const uint32_t s_tiles = smem_u32(smem);
   const uint32_t s_bar = s_tiles + G::WARP_BYTES;
   if (lane == 0) {
@@ -115,8 +135,8 @@ __global__ void __launch_bounds__(32) digest_tile_kernel(const __grid_constant__
   uint32_t h[A::NS];
   A::init(h);
   PipeState ps;
-  tile_segment<A, K, NST>(&tmap, blockIdx.x * 32u, p.len, 0u, nch, nch, h, s_tiles, s_bar, lane, ps, p.one);
-  finish_group<A>(p, blockIdx.x, lane, h);
+  tile_segment<A, K, NST>(&tmap, group * 32u, p.len, 0u, nch, nch, h, s_tiles, s_bar, lane, ps, p.one);
+  finish_group<A>(p, group, lane, h);
 }
 
 // Few, large messages (fewer groups than SM sub-partitions): chain warp + schedule helper warp per group.
@@ -125,6 +145,8 @@ __global__ void __launch_bounds__(64) digest_assist_kernel(const __grid_constant
   extern __shared__ __align__(1024) unsigned char smem[];
   using G = Tiles<K, NST>;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t group;
+  if (!spread_group(p, &group)) return;
   const uint32_t s_tiles = smem_u32(smem);
   const uint32_t s_ring = s_tiles + G::WARP_BYTES;
   const uint32_t s_bar = s_ring + SS * Assist<A>::WPB * 128;
@@ -139,12 +161,12 @@ __global__ void __launch_bounds__(64) digest_assist_kernel(const __grid_constant
   const uint32_t r = (uint32_t)(p.len & 63u);
   const uint32_t total = (uint32_t)(p.len >> 6) + (r < 56 ? 1u : 2u);
   if (warp == 1) {
-    assist_produce<A, K, NST, SS>(&tmap, blockIdx.x * 32u, p.len, nch, s_tiles, s_bar, s_ring, lane, p.one);
+    assist_produce<A, K, NST, SS>(&tmap, group * 32u, p.len, nch, s_tiles, s_bar, s_ring, lane, p.one);
   } else {
     uint32_t h[A::NS];
     A::init(h);
     assist_consume<A, SS>(total, h, smem + G::WARP_BYTES, lane, p.one);
-    finish_group<A>(p, blockIdx.x, lane, h);
+    finish_group<A>(p, group, lane, h);
   }
 }
 
@@ -306,12 +328,35 @@ __global__ void __launch_bounds__(256) synth_kernel(uint8_t* __restrict__ dst, u
 }
 
 // ------------------------------------------------------------------------------------ dispatch
+// cudaFuncSetAttribute is per device: remember, per kernel instantiation, which devices have been set up.
+template <class KernelPtr>
+static cudaError_t allow_smem(KernelPtr kernel, bool* done /* [64] */, int bytes) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+  if (!done[dev]) {
+    if (bytes > 48 * 1024) {
+      e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+      if (e != cudaSuccess) return e;
+    }
+    // Every digest kernel asks for the same (maximum) shared-memory carve-out: an SM has to drain before its
+    // L1 / shared split can change, which serialised long kernels of different submits that met on one SM.
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+    if (e != cudaSuccess) return e;
+    done[dev] = true;
+  }
+  return cudaSuccess;
+}
+
 using launch_fn = cudaError_t (*)(const DigestArgs&, cudaStream_t);
 
 template <class A, int CH, int NST>
 cudaError_t launch_variant(const DigestArgs& a, cudaStream_t st) {
-  constexpr int smem = Staging<CH, NST>::WARP_BYTES;  // <= 34 KiB for every compiled variant: no opt-in needed
-  static_assert(smem <= 48 * 1024, "bulk staging variant needs the dynamic shared memory opt-in");
+  constexpr int smem = Staging<CH, NST>::WARP_BYTES;  // <= 34 KiB for every compiled variant
+  static bool done[64] = {};
+  cudaError_t e0 = allow_smem(digest_kernel<A, CH, NST>, done, smem);
+  if (e0 != cudaSuccess) return e0;
   const uint32_t grid = (a.n + 31u) / 32u;
   digest_kernel<A, CH, NST><<<grid, 32, smem, st>>>(a);
   return cudaGetLastError();
@@ -360,32 +405,21 @@ struct TileOpts {
 };
 static TileOpts g_opts;
 
+// Launches with at most one group per SM ask for this much shared memory although they need less: then no more
+// than two such CTAs (of any concurrently running digest kernel) fit on an SM, so their at most four long-running
+// warps get a sub-partition each.  Without it the block scheduler stacked chains of different submits on the same
+// sub-partitions (SHA-256 kernels of 1.05 s stretched to 2.1 and 3.1 s) while most of the chip was idle.
+constexpr int kRoomySmem = 112 * 1024;
+
 using tile_fn = cudaError_t (*)(const CUtensorMap&, const TileArgs&, uint32_t grid, uint32_t block, size_t smem, cudaStream_t);
 
-// cudaFuncSetAttribute is per device: remember, per kernel instantiation, which devices have been set up.
-template <class KernelPtr>
-static cudaError_t allow_smem(KernelPtr kernel, bool* done /* [64] */, int bytes) {
-  int dev = 0;
-  cudaError_t e = cudaGetDevice(&dev);
-  if (e != cudaSuccess) return e;
-  if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
-  if (!done[dev]) {
-    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-    if (e != cudaSuccess) return e;
-    done[dev] = true;
-  }
-  return cudaSuccess;
-}
-
 template <class A, int K, int NST>
-cudaError_t launch_tile(const CUtensorMap& m, const TileArgs& a, uint32_t grid, uint32_t, size_t, cudaStream_t st) {
+cudaError_t launch_tile(const CUtensorMap& m, const TileArgs& a, uint32_t grid, uint32_t, size_t pad, cudaStream_t st) {
   constexpr int smem = Tiles<K, NST>::WARP_BYTES + 8 * NST;
   static bool done[64] = {};
-  if (smem > 48 * 1024) {
-    cudaError_t e = allow_smem(digest_tile_kernel<A, K, NST>, done, smem);
-    if (e != cudaSuccess) return e;
-  }
-  digest_tile_kernel<A, K, NST><<<grid, 32, smem, st>>>(m, a);
+  cudaError_t e0 = allow_smem(digest_tile_kernel<A, K, NST>, done, smem > kRoomySmem ? smem : kRoomySmem);
+  if (e0 != cudaSuccess) return e0;
+  digest_tile_kernel<A, K, NST><<<grid, 32, pad > (size_t)smem ? pad : (size_t)smem, st>>>(m, a);
   return cudaGetLastError();
 }
 
@@ -399,12 +433,12 @@ cudaError_t launch_sliced(const CUtensorMap& m, const TileArgs& a, uint32_t grid
 }
 
 template <class A, int K, int NST, int SS>
-cudaError_t launch_assist(const CUtensorMap& m, const TileArgs& a, uint32_t grid, uint32_t, size_t, cudaStream_t st) {
+cudaError_t launch_assist(const CUtensorMap& m, const TileArgs& a, uint32_t grid, uint32_t, size_t pad, cudaStream_t st) {
   constexpr int smem = Tiles<K, NST>::WARP_BYTES + SS * Assist<A>::WPB * 128 + 8 * NST;
   static bool done[64] = {};
-  cudaError_t e0 = allow_smem(digest_assist_kernel<A, K, NST, SS>, done, smem);
+  cudaError_t e0 = allow_smem(digest_assist_kernel<A, K, NST, SS>, done, smem > kRoomySmem ? smem : kRoomySmem);
   if (e0 != cudaSuccess) return e0;
-  digest_assist_kernel<A, K, NST, SS><<<grid, 64, smem, st>>>(m, a);
+  digest_assist_kernel<A, K, NST, SS><<<grid, 64, pad > (size_t)smem ? pad : (size_t)smem, st>>>(m, a);
   return cudaGetLastError();
 }
 
@@ -488,21 +522,34 @@ static int launch_uniform(int ai, const void* d_base, uint64_t stride, uint64_t 
   if (pl.path == 1) return 1;
   CUtensorMap tmap;
   if (!make_tmap(&tmap, d_base, len, stride, n)) return 1;
-  TileArgs a{len, n, pl.segc, pl.nseg, d_out, d_expected, d_ok_bits, 1u};
+  TileArgs a{len, n, pl.segc, pl.nseg, d_out, d_expected, d_ok_bits, 1u, 0u};
+  uint32_t grid = pl.grid;
+  size_t pad = 0;
+  if (pl.path != 3) {  // few CTAs: pad to one per SM and rotate by a per-launch salt (see spread_group)
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (grid <= (uint32_t)sms) {
+      static std::atomic<uint32_t> launches{0};
+      a.salt = (launches.fetch_add(1) * 37u) % (uint32_t)sms;
+      grid = (uint32_t)sms;
+      pad = kRoomySmem;
+    }
+  }
   if (pl.path == 4) {
     cudaError_t e;
     switch (g_opts.assist_variant) {
-      case 1: e = ai == 0 ? launch_assist<Sha1, 4, 2, 4>(tmap, a, pl.grid, 64, 0, st) : launch_assist<Sha256, 4, 2, 4>(tmap, a, pl.grid, 64, 0, st); break;
-      case 2: e = ai == 0 ? launch_assist<Sha1, 4, 4, 4>(tmap, a, pl.grid, 64, 0, st) : launch_assist<Sha256, 4, 4, 4>(tmap, a, pl.grid, 64, 0, st); break;
-      case 3: e = ai == 0 ? launch_assist<Sha1, 4, 4, 7>(tmap, a, pl.grid, 64, 0, st) : launch_assist<Sha256, 4, 4, 7>(tmap, a, pl.grid, 64, 0, st); break;
-      case 4: e = ai == 0 ? launch_assist<Sha1, 2, 4, 2>(tmap, a, pl.grid, 64, 0, st) : launch_assist<Sha256, 2, 4, 2>(tmap, a, pl.grid, 64, 0, st); break;
-      default: e = ai == 0 ? launch_assist<Sha1, 2, 2, 4>(tmap, a, pl.grid, 64, 0, st) : launch_assist<Sha256, 2, 2, 4>(tmap, a, pl.grid, 64, 0, st); break;
+      case 1: e = ai == 0 ? launch_assist<Sha1, 4, 2, 4>(tmap, a, grid, 64, pad, st) : launch_assist<Sha256, 4, 2, 4>(tmap, a, grid, 64, pad, st); break;
+      case 2: e = ai == 0 ? launch_assist<Sha1, 4, 4, 4>(tmap, a, grid, 64, pad, st) : launch_assist<Sha256, 4, 4, 4>(tmap, a, grid, 64, pad, st); break;
+      case 3: e = ai == 0 ? launch_assist<Sha1, 4, 4, 7>(tmap, a, grid, 64, pad, st) : launch_assist<Sha256, 4, 4, 7>(tmap, a, grid, 64, pad, st); break;
+      case 4: e = ai == 0 ? launch_assist<Sha1, 2, 4, 2>(tmap, a, grid, 64, pad, st) : launch_assist<Sha256, 2, 4, 2>(tmap, a, grid, 64, pad, st); break;
+      default: e = ai == 0 ? launch_assist<Sha1, 2, 2, 4>(tmap, a, grid, 64, pad, st) : launch_assist<Sha256, 2, 2, 4>(tmap, a, grid, 64, pad, st); break;
     }
     return e == cudaSuccess ? TH_OK : TH_ECUDA;
   }
   const TileVariant& v = g_tile_variants[pl.variant];
   cudaError_t e = pl.path == 3 ? v.sliced[ai](tmap, a, pl.grid, pl.block, pl.smem, st)
-                               : v.tile[ai](tmap, a, pl.grid, 32, 0, st);
+                               : v.tile[ai](tmap, a, grid, 32, pad, st);
   return e == cudaSuccess ? TH_OK : TH_ECUDA;
 }
 

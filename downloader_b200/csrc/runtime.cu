@@ -15,6 +15,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <deque>
+#include <map>
 #include <mutex>
 #include <numeric>
 #include <string>
@@ -38,6 +39,8 @@ struct JobBuf {
   uint8_t* h = nullptr;
   uint8_t* d = nullptr;
   size_t bytes = 0;
+  bool from_arena = false;     // carved out of the per-GPU staging arena (no CUDA allocation on the submit path)
+  size_t arena_off = 0;
   static size_t bytes_for(size_t n) { return align_up(n * (8 + 8 + 4 + 20 + 20 + 16 + 32) + ((n + 31) / 32) * 4 + 9 * 256, 256); }
   size_t o_off(size_t) const { return 0; }
   size_t o_len(size_t n) const { return align_up(n * 8, 256); }
@@ -73,6 +76,8 @@ struct Ticket {
   JobBuf* jb = nullptr;
   uint64_t slot_id = 0;        // 0 = device-resident submit
   cudaEvent_t ev_done = nullptr;
+  cudaEvent_t ev_ready = nullptr;  // inputs (payload + descriptors) on the device; timing-enabled
+  double times_ms[7] = {-1, -1, -1, -1, -1, -1, -1};  // since th_init: ready, then start / end per digest
   cudaEvent_t ev_k0[3] = {nullptr, nullptr, nullptr}, ev_k1[3] = {nullptr, nullptr, nullptr};
   th_done_cb cb = nullptr;
   void* user = nullptr;
@@ -93,7 +98,9 @@ struct StreamSet {
 struct Gpu {
   int dev = -1;
   cudaStream_t s_copy = nullptr, s_misc = nullptr;  // H2D copies; synchronous odd jobs (ETag combine)
+  cudaEvent_t ev_epoch = nullptr;                   // recorded in th_init: origin of th_ticket_timing
   StreamSet sets[kStreamSets];
+  int n_sets = kStreamSets;     // TRITONHASH_STREAM_SETS (1..10) narrows the rotation
   uint64_t next_stream[3] = {0, 0, 0};  // each digest rotates over its own 10 streams, whatever mix of submits arrives
   uint8_t* ring_h = nullptr;
   uint8_t* ring_d = nullptr;
@@ -101,6 +108,13 @@ struct Gpu {
   size_t head = 0, tail = 0;   // ring allocator: live region is [head, tail) modulo wrap
   std::deque<Slot> slots;      // FIFO, oldest first
   std::vector<JobBuf*> free_jobs;
+  // Staging arena: one pinned + one device block allocated in th_init, carved first-fit into job buffers.
+  // cudaMalloc / cudaHostAlloc on the submit path would wait for every running kernel (they synchronise the
+  // device), which serialises exactly the long kernels that must overlap; they remain only as the overflow path.
+  uint8_t* arena_h = nullptr;
+  uint8_t* arena_d = nullptr;
+  size_t arena_bytes = 0;
+  std::map<size_t, size_t> arena_free;  // offset -> length, coalesced
   th_stats st{};
 };
 
@@ -128,7 +142,32 @@ int cuda_fail(th_ctx* c, cudaError_t e, const char* what) {
     if (e__ != cudaSuccess) return cuda_fail((ctx), e__, #call);  \
   } while (0)
 
+void put_job(Gpu& g, JobBuf* jb) {
+  if (!jb->from_arena) { g.free_jobs.push_back(jb); return; }
+  size_t off = jb->arena_off, len = jb->bytes;
+  delete jb;
+  auto next = g.arena_free.lower_bound(off);
+  if (next != g.arena_free.begin()) {
+    auto prev = std::prev(next);
+    if (prev->first + prev->second == off) { off = prev->first; len += prev->second; g.arena_free.erase(prev); }
+  }
+  if (next != g.arena_free.end() && off + len == next->first) { len += next->second; g.arena_free.erase(next); }
+  g.arena_free[off] = len;
+}
+
 JobBuf* get_job(th_ctx* c, Gpu& g, size_t n, int* rc) {
+  const size_t need = JobBuf::bytes_for(n);
+  for (auto it = g.arena_free.begin(); it != g.arena_free.end(); ++it) {
+    if (it->second >= need) {
+      JobBuf* jb = new JobBuf();
+      jb->cap_n = n; jb->bytes = need; jb->from_arena = true; jb->arena_off = it->first;
+      jb->h = g.arena_h + it->first; jb->d = g.arena_d + it->first;
+      const size_t rest = it->second - need, off = it->first;
+      g.arena_free.erase(it);
+      if (rest) g.arena_free[off + need] = rest;
+      return jb;
+    }
+  }
   for (size_t i = 0; i < g.free_jobs.size(); i++) {
     if (g.free_jobs[i]->cap_n >= n) {
       JobBuf* jb = g.free_jobs[i];
@@ -201,8 +240,8 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
   if (ulen >= 1024 && ulen < (1ull << 31) && (ustride & 15) == 0 && ustride >= ulen && (n == 1 || msgs[1].offset > msgs[0].offset)) {
     m = 1;
     while (m < n && msgs[m].length == ulen && msgs[m].offset == msgs[0].offset + m * ustride) m++;
-    if (m < n) m &= ~(size_t)31;
-    if (m < 64 && m < n) m = 0;
+    if (m < n && expected) m &= ~(size_t)31;  // keep the verify bitfield split on a word boundary
+    if (m < n && m < 64 && m * ulen < (8u << 20)) m = 0;  // a short prefix of small messages is not worth a launch
   }
   const size_t rest = n - m;
   // Length bucketing for the remainder: a warp runs as long as its longest message, so lanes are dealt
@@ -228,8 +267,9 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
   CU(c, cudaMemcpyAsync(jb->d, jb->h, desc_bytes, cudaMemcpyHostToDevice, g.s_copy));
   g.st.h2d_bytes += desc_bytes;
   cudaEvent_t ev_in;
-  CU(c, cudaEventCreateWithFlags(&ev_in, cudaEventDisableTiming));
+  CU(c, cudaEventCreate(&ev_in));
   CU(c, cudaEventRecord(ev_in, g.s_copy));
+  t->ev_ready = ev_in;
 
   const uint64_t* d_off = reinterpret_cast<const uint64_t*>(jb->d + jb->o_off(n)) + m;
   const uint64_t* d_len = reinterpret_cast<const uint64_t*>(jb->d + jb->o_len(n)) + m;
@@ -245,7 +285,7 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
 
   for (int a = 0; a < 3; a++) {
     if (!(mask & (1u << a))) continue;
-    cudaStream_t st = g.sets[g.next_stream[a]++ % kStreamSets].alg[a];
+    cudaStream_t st = g.sets[g.next_stream[a]++ % (uint64_t)g.n_sets].alg[a];
     tstream[a] = st;
     CU(c, cudaStreamWaitEvent(st, ev_in, 0));
     int rc = TH_OK;
@@ -256,24 +296,43 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
     uint32_t* d_ok = (a == 0 && expected) ? reinterpret_cast<uint32_t*>(jb->d + jb->o_ok(n)) : nullptr;
     if (d_ok && use_order) CU(c, cudaMemsetAsync(d_ok + m / 32, 0, ok_bytes - (m / 32) * 4, st));
     CU(c, cudaEventRecord(t->ev_k0[a], st));
+    cudaEvent_t ev_rest = nullptr;
     for (int part = 0; part < 2 && rc == TH_OK; part++) {
       const bool uni = part == 0;
       const size_t cnt = uni ? m : rest;
       if (cnt == 0) continue;
       const size_t first = uni ? 0 : m;
-      const uint8_t* pb = uni ? d_uni : d_base;
-      const uint64_t* po = uni ? nullptr : d_off;
-      const uint64_t* pl = uni ? nullptr : d_len;
-      const uint32_t* pr = uni ? nullptr : d_ord;
+      // the odd tail (short last piece / part) of a mostly equal-length batch runs beside the prefix on another
+      // stream of this digest's rotation; a single tail message is itself an "equal-length batch" of one
+      cudaStream_t ps = st;
+      if (!uni && m > 0 && !(d_ok && use_order)) {  // (the bitfield memset above is ordered on st only)
+        ps = g.sets[g.next_stream[a]++ % (uint64_t)g.n_sets].alg[a];
+        CU(c, cudaStreamWaitEvent(ps, ev_in, 0));
+      }
+      const bool lone = !uni && cnt == 1 && msgs[first].length >= 1024;
+      const uint8_t* pb = uni ? d_uni : (lone ? d_base + msgs[first].offset : d_base);
+      const uint64_t* po = (uni || lone) ? nullptr : d_off;
+      const uint64_t* pl = (uni || lone) ? nullptr : d_len;
+      const uint32_t* pr = (uni || lone) ? nullptr : d_ord;
+      const uint64_t pstride = lone ? ((msgs[first].length + 15) & ~15ull) : ustride;
+      const uint64_t plen = lone ? msgs[first].length : ulen;
       uint8_t* o = d_out + first * dlen[a];
       if (a == 0)
-        rc = th_sha1_batch(pb, po, pl, pr, ustride, ulen, (uint32_t)cnt, o, d_exp ? d_exp + first * 20 : nullptr,
-                           d_ok ? d_ok + first / 32 : nullptr, st);
+        rc = th_sha1_batch(pb, po, pl, pr, pstride, plen, (uint32_t)cnt, o, d_exp ? d_exp + first * 20 : nullptr,
+                           d_ok ? d_ok + first / 32 : nullptr, ps);
       else if (a == 1)
-        rc = th_md5_batch(pb, po, pl, pr, ustride, ulen, (uint32_t)cnt, o, st);
+        rc = th_md5_batch(pb, po, pl, pr, pstride, plen, (uint32_t)cnt, o, ps);
       else
-        rc = th_sha256_batch(pb, po, pl, pr, ustride, ulen, (uint32_t)cnt, o, st);
+        rc = th_sha256_batch(pb, po, pl, pr, pstride, plen, (uint32_t)cnt, o, ps);
       g.st.launches += 1;
+      if (ps != st && rc == TH_OK) {
+        CU(c, cudaEventCreateWithFlags(&ev_rest, cudaEventDisableTiming));
+        CU(c, cudaEventRecord(ev_rest, ps));
+      }
+    }
+    if (ev_rest) {
+      CU(c, cudaStreamWaitEvent(st, ev_rest, 0));
+      CU(c, cudaEventDestroy(ev_rest));
     }
     if (rc != TH_OK) {
       if (rc == TH_ECUDA) return cuda_fail(c, cudaGetLastError(), "digest kernel launch");
@@ -296,7 +355,6 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
       joins.push_back(ev_a);
     }
   }
-  CU(c, cudaEventDestroy(ev_in));
   cudaStream_t sp = tstream[primary];
   for (cudaEvent_t ev : joins) {
     CU(c, cudaStreamWaitEvent(sp, ev, 0));
@@ -326,6 +384,7 @@ int validate(const th_msg* msgs, size_t n, uint32_t mask, size_t limit) {
 
 void free_ticket_events(Ticket* t) {
   if (t->ev_done) cudaEventDestroy(t->ev_done);
+  if (t->ev_ready) cudaEventDestroy(t->ev_ready);
   for (int a = 0; a < 3; a++) {
     if (t->ev_k0[a]) cudaEventDestroy(t->ev_k0[a]);
     if (t->ev_k1[a]) cudaEventDestroy(t->ev_k1[a]);
@@ -347,6 +406,10 @@ int th_init(const int* gpu_ids, int n_gpus, size_t ring_bytes_per_gpu, th_ctx** 
   for (int i = 0; i < n_gpus; i++) {
     Gpu& g = c->gpus[(size_t)i];
     g.dev = gpu_ids ? gpu_ids[i] : i;
+    if (const char* e = getenv("TRITONHASH_STREAM_SETS")) {
+      const int v = atoi(e);
+      if (v >= 1 && v <= kStreamSets) g.n_sets = v;
+    }
     cudaDeviceProp prop{};
     if (g.dev < 0 || g.dev >= count || cudaGetDeviceProperties(&prop, g.dev) != cudaSuccess || prop.major < 10) {
       th_shutdown(c);
@@ -355,12 +418,20 @@ int th_init(const int* gpu_ids, int n_gpus, size_t ring_bytes_per_gpu, th_ctx** 
     cudaError_t e = cudaSetDevice(g.dev);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&g.s_copy, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&g.s_misc, cudaStreamNonBlocking);
-    for (int k = 0; k < kStreamSets && e == cudaSuccess; k++)
+    if (e == cudaSuccess) e = cudaEventCreate(&g.ev_epoch);
+    if (e == cudaSuccess) e = cudaEventRecord(g.ev_epoch, g.s_copy);
+    for (int k = 0; k < g.n_sets && e == cudaSuccess; k++)
       for (int a = 0; a < 3 && e == cudaSuccess; a++) e = cudaStreamCreateWithFlags(&g.sets[k].alg[a], cudaStreamNonBlocking);
     if (e == cudaSuccess && ring_bytes_per_gpu) {
       g.ring_bytes = align_up(ring_bytes_per_gpu, kRingAlign);
       e = cudaHostAlloc((void**)&g.ring_h, g.ring_bytes, cudaHostAllocPortable);
       if (e == cudaSuccess) e = cudaMalloc((void**)&g.ring_d, g.ring_bytes);
+    }
+    if (e == cudaSuccess) {  // ~108 bytes of descriptors + digests per message; 1/128 of the ring covers 16 KiB messages
+      g.arena_bytes = align_up(std::max<size_t>(64u << 20, g.ring_bytes / 128), 256);
+      e = cudaHostAlloc((void**)&g.arena_h, g.arena_bytes, cudaHostAllocPortable);
+      if (e == cudaSuccess) e = cudaMalloc((void**)&g.arena_d, g.arena_bytes);
+      if (e == cudaSuccess) g.arena_free[0] = g.arena_bytes;
     }
     if (e != cudaSuccess) {
       int rc = (e == cudaErrorMemoryAllocation) ? TH_ENOMEM : TH_ECUDA;
@@ -379,17 +450,20 @@ int th_shutdown(th_ctx* c) {
     cudaSetDevice(g.dev);
     cudaDeviceSynchronize();
     for (auto* jb : g.free_jobs) { cudaFreeHost(jb->h); cudaFree(jb->d); delete jb; }
+    if (g.arena_h) cudaFreeHost(g.arena_h);
+    if (g.arena_d) cudaFree(g.arena_d);
     if (g.ring_h) cudaFreeHost(g.ring_h);
     if (g.ring_d) cudaFree(g.ring_d);
     if (g.s_copy) cudaStreamDestroy(g.s_copy);
     if (g.s_misc) cudaStreamDestroy(g.s_misc);
+    if (g.ev_epoch) cudaEventDestroy(g.ev_epoch);
     for (auto& ss : g.sets)
       for (auto& s : ss.alg) if (s) cudaStreamDestroy(s);
   }
   for (auto& kv : c->tickets) {
     Ticket* t = kv.second;
     free_ticket_events(t);
-    if (t->jb) { cudaFreeHost(t->jb->h); cudaFree(t->jb->d); delete t->jb; }
+    if (t->jb) { if (!t->jb->from_arena) { cudaFreeHost(t->jb->h); cudaFree(t->jb->d); } delete t->jb; }
     delete t;
   }
   delete c;
@@ -474,7 +548,7 @@ static int submit_common(th_ctx* c, int gpu, Slot* slot, const void* d_base_user
   rc = enqueue(c, g, t, d_base, slot, msgs, n, mask, t->has_expected ? expected : nullptr);
   if (rc != TH_OK) {
     free_ticket_events(t);
-    g.free_jobs.push_back(jb);
+    put_job(g, jb);
     delete t;
     return rc;
   }
@@ -520,14 +594,28 @@ static int wait_locked(th_ctx* c, Ticket* t) {
     if (e != cudaSuccess) t->status = cuda_fail(c, e, "cudaEventSynchronize(ticket)");
   }
   if (!t->timed && t->status == TH_OK) {
+    Gpu& g = c->gpus[(size_t)t->gpu];
+    float ms = 0.f;
+    if (t->ev_ready && cudaEventElapsedTime(&ms, g.ev_epoch, t->ev_ready) == cudaSuccess) t->times_ms[0] = ms;
     for (int a = 0; a < 3; a++) {
-      float ms = 0.f;
-      if (t->ev_k0[a] && cudaEventElapsedTime(&ms, t->ev_k0[a], t->ev_k1[a]) == cudaSuccess)
-        c->gpus[(size_t)t->gpu].st.kernel_ms += ms;
+      if (!t->ev_k0[a]) continue;
+      if (cudaEventElapsedTime(&ms, t->ev_k0[a], t->ev_k1[a]) == cudaSuccess) g.st.kernel_ms += ms;
+      if (cudaEventElapsedTime(&ms, g.ev_epoch, t->ev_k0[a]) == cudaSuccess) t->times_ms[1 + 2 * a] = ms;
+      if (cudaEventElapsedTime(&ms, g.ev_epoch, t->ev_k1[a]) == cudaSuccess) t->times_ms[2 + 2 * a] = ms;
     }
     t->timed = true;
   }
   return t->status;
+}
+
+int th_ticket_timing(th_ctx* c, th_ticket id, double* ms7) {
+  if (!c || !ms7) return TH_EINVAL;
+  std::lock_guard<std::mutex> lk(c->mu);
+  auto it = c->tickets.find(id);
+  if (it == c->tickets.end()) return TH_ESTATE;
+  int rc = wait_locked(c, it->second);
+  for (int i = 0; i < 7; i++) ms7[i] = it->second->times_ms[i];
+  return rc;
 }
 
 int th_wait(th_ctx* c, th_ticket id) {
@@ -555,7 +643,7 @@ int th_result(th_ctx* c, th_ticket id, uint8_t* sha1, uint8_t* md5, uint8_t* sha
   }
   Gpu& g = c->gpus[(size_t)t->gpu];
   free_ticket_events(t);
-  g.free_jobs.push_back(jb);
+  put_job(g, jb);
   c->tickets.erase(it);
   delete t;
   reap(c, g, false);

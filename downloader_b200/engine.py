@@ -102,6 +102,12 @@ class Engine:
         check(rc, "th_submit_device", self._ctx)
         return t.value
 
+    def timing(self, ticket: int) -> list:
+        """[ready, sha1 start, sha1 end, md5 start, md5 end, sha256 start, sha256 end] in ms since th_init."""
+        out = (C.c_double * 7)()
+        check(self._L.th_ticket_timing(self._ctx, ticket, out), "th_ticket_timing", self._ctx)
+        return list(out)
+
     def wait(self, ticket: int) -> None:
         check(self._L.th_wait(self._ctx, ticket), "th_wait", self._ctx)
 

@@ -101,6 +101,11 @@ int th_submit_device(th_ctx* ctx, int gpu, const void* d_base, const th_msg* msg
                      uint32_t alg_mask, const uint8_t* expected_sha1, th_done_cb cb, void* user,
                      th_ticket* out);
 
+/* Device-side timeline of a ticket in milliseconds since th_init (waits for the ticket; call before th_result):
+ * ms7[0] inputs on the device; ms7[1], ms7[2] start / end of the SHA-1 kernel(s); [3], [4] MD5; [5], [6] SHA-256;
+ * -1 where a digest was not requested.  Used to see copy / kernel overlap of the host path (tools/config4.py). */
+int th_ticket_timing(th_ctx* ctx, th_ticket ticket, double* ms7);
+
 /* Blocks until the ticket's digests are in host memory. */
 int th_wait(th_ctx* ctx, th_ticket ticket);
 /* Copies results out (any pointer may be NULL) and retires the ticket.  Waits if needed.

@@ -5,8 +5,8 @@
 torrent pieces (piece length from {1, 2, 4} MiB, SHA-1) and as S3 parts (part size from {8, 16, 32, 64} MiB,
 MD5 + SHA-256), short last piece / part included.  File bytes stream through the pinned ring in slots of
 --slot-mib; every slot crosses PCIe once and is submitted twice.  To avoid regenerating ~220 GiB, file content
-is periodic: every slot holds the same synthetic window (filled once, untimed), so digests of equal
-(offset, length) ranges repeat — which the run checks — and slot 0 is checked against the CPU oracle.
+is periodic (one 64 MiB synthetic pattern, written into the whole ring once, untimed; slots are 64 MiB-aligned),
+so digests of equal (offset, length) ranges repeat — which the run checks — and slot 0 is checked against the CPU oracle.
 Timed region = acquire + submit + result for every slot of every file (H2D, kernels, D2H inside).
 Prints one JSON line (bytes counted once per file).
 """
@@ -42,9 +42,11 @@ def main():
     n_slots = (a.ring_gib * GiB) // slot_bytes
     L = _capi.lib()
     torch.cuda.set_device(0)
-    win = torch.empty(slot_bytes, dtype=torch.uint8, device="cuda")
-    L.th_synth_fill(win.data_ptr(), 0, 1, slot_bytes, slot_bytes, 11, None)
+    PERIOD = 64 * MiB  # ring content repeats every 64 MiB, so any 64 MiB-aligned slot holds the same stream
+    pat = torch.empty(PERIOD, dtype=torch.uint8, device="cuda")
+    L.th_synth_fill(pat.data_ptr(), 0, 1, PERIOD, PERIOD, 11, None)
     torch.cuda.synchronize()
+    win = pat.repeat(slot_bytes // PERIOD)
     eng = Engine([0], ring_bytes=n_slots * slot_bytes)
     held = []
     for _ in range(n_slots):  # every slot gets the same window; contents persist across re-acquisition
@@ -66,18 +68,24 @@ def main():
     pending = []
 
     prof = {"retire": 0.0, "acquire": 0.0, "submit": 0.0}
+    gpu_tl = []  # per slot: part MiB, copy done, sha1 start/end, md5 start/end, sha256 start/end (s since th_init)
+    timeline = []  # (part MiB, seconds since start) at which each slot's results were in hand
 
     def retire(k):
         while len(pending) > k:
             tp, np_, tq, nq, key = pending.pop(0)
+            tm_p, tm_q = eng.timing(tp), eng.timing(tq)
+            gpu_tl.append([key[2] // MiB] + [round(x / 1e3, 2) for x in (tm_p[0], tm_p[1], tm_p[2], tm_q[3], tm_q[4], tm_q[5], tm_q[6])])
             t_ = time.perf_counter()
             rp = eng.result(tp, np_, ALG_SHA1)
             rq = eng.result(tq, nq, ALG_MD5 | ALG_SHA256)
             prof["retire"] += time.perf_counter() - t_
+            timeline.append((key[2] // MiB, round(time.perf_counter() - T0, 2)))
             ref = first.setdefault(key, (rp, rq))
             assert (ref[0][ALG_SHA1] == rp[ALG_SHA1]).all() and (ref[1][ALG_SHA256] == rq[ALG_SHA256]).all()
             assert (ref[1][ALG_MD5] == rq[ALG_MD5]).all()
 
+    global T0
     T0 = time.perf_counter()
     for size, plen, psize in zip(sizes, plens, psizes):  # the batch is pipelined ACROSS files: no drain at file ends
         pos = 0
@@ -85,7 +93,7 @@ def main():
             nb = min(slot_bytes, size - pos)
             retire(n_slots - 1)
             t_ = time.perf_counter()
-            sid, _ = eng.ring_acquire(slot_bytes)  # full slot, so offsets stay slot-aligned and hold the window
+            sid, _ = eng.ring_acquire(-(-nb // PERIOD) * PERIOD)  # 64 MiB-aligned, so every slot holds the same stream
             prof["acquire"] += time.perf_counter() - t_
             po, pl = msgs(nb, plen)
             qo, ql = msgs(nb, psize)
@@ -114,7 +122,7 @@ def main():
                       "e2e_GBps": round(total / T / 1e9, 2),
                       "h2d_GBps": round((s1["h2d_bytes"] - s0["h2d_bytes"]) / T / 1e9, 2),
                       "launches": s1["launches"] - s0["launches"], "kernel_ms_sum": round(s1["kernel_ms"] - s0["kernel_ms"], 1),
-                      "host_seconds": {k: round(v, 2) for k, v in prof.items()}, "files": per_file}))
+                      "host_seconds": {k: round(v, 2) for k, v in prof.items()}, "slot_done_timeline": timeline, "gpu_timeline": gpu_tl, "files": per_file}))
     eng.close()
 
 
