@@ -183,6 +183,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="sha1_pieces", choices=sorted(WORKLOADS))
     ap.add_argument("--messages", type=int, default=0, help="override messages per GPU (not the BASELINE config)")
+    ap.add_argument("--strong", action="store_true", help="divide the workload's messages over the ranks (BASELINE config 3 as stated) instead of giving each GPU all of them")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--e2e-slots", type=int, default=8)
@@ -208,6 +209,9 @@ def main():
     algs, n, ln, desc = WORKLOADS[args.workload]
     if args.messages:
         n = args.messages
+    if args.strong:
+        n = max(32, n // world)
+        desc += " / %d ranks (strong scaling)" % world
     hbm_peak, sm_max_mhz, peak_src = load_peaks()
     total_bytes = n * ln
     first_msg = rank * n  # shard by index: rank r owns messages [r*n, (r+1)*n)
@@ -390,7 +394,7 @@ def main():
 
     line = {
         "metric": METRIC, "value": round(value, 3), "unit": "GB/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True, "scaling": "strong" if args.strong else "weak",
         "vs_baseline": None, "dtype": "u32", "data": "synthetic",
         "config": {"workload": desc, "algs": algs, "messages_per_gpu": n, "message_bytes": ln,
                    "l2": "inputs (%.1f GiB per GPU) exceed the 126 MB L2; no flush" % (total_bytes / 2**30),

@@ -430,3 +430,17 @@ def test_messages_longer_than_512_mib_and_2_gib(torch, L):
     assert L.th_md5_batch(d.data_ptr(), None, None, None, ln, ln, 1, o.data_ptr(), None) == 0
     torch.cuda.synchronize()
     assert o.cpu().numpy().tobytes() == hashlib.md5(d.cpu().numpy()).digest()
+
+
+def test_ticket_timing_is_a_consistent_device_timeline(eng):
+    """th_ticket_timing: inputs ready <= kernel start <= kernel end for requested digests, -1 for the others."""
+    import ctypes as C
+    ln = 1 << 20
+    slot, view = eng.ring_acquire(4 * ln)
+    view[:] = 7
+    t = eng.submit(slot, np.arange(4, dtype=np.uint64) * ln, np.full(4, ln, np.uint64), SHA1 | SHA256)
+    tm = eng.timing(t)
+    assert tm[0] >= 0 and tm[0] <= tm[1] <= tm[2] and tm[0] <= tm[5] <= tm[6]
+    assert tm[3] == -1 and tm[4] == -1
+    r = eng.result(t, 4, SHA1 | SHA256)
+    assert r[SHA1][0].tobytes() == hashlib.sha1(bytes([7]) * ln).digest()
