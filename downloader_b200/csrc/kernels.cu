@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(64) digest_assist_kernel(const __grid_constant
 // sub-partitions stay equally loaded until the end, instead of 4,4,3,3 warps finishing at different
 // times.  Chaining values travel through shared memory; done[g] counts finished segments.
 template <class A, int K, int NST>
-__global__ void __launch_bounds__(512, 1) digest_sliced_kernel(const __grid_constant__ CUtensorMap tmap,
+__global__ void __launch_bounds__(A::SLICED_BOUND, 1) digest_sliced_kernel(const __grid_constant__ CUtensorMap tmap,
                                                                const TileArgs p) {
   extern __shared__ __align__(1024) unsigned char smem[];
   using G_ = Tiles<K, NST>;
