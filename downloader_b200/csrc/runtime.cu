@@ -296,43 +296,56 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
     uint32_t* d_ok = (a == 0 && expected) ? reinterpret_cast<uint32_t*>(jb->d + jb->o_ok(n)) : nullptr;
     if (d_ok && use_order) CU(c, cudaMemsetAsync(d_ok + m / 32, 0, ok_bytes - (m / 32) * 4, st));
     CU(c, cudaEventRecord(t->ev_k0[a], st));
-    cudaEvent_t ev_rest = nullptr;
-    for (int part = 0; part < 2 && rc == TH_OK; part++) {
-      const bool uni = part == 0;
-      const size_t cnt = uni ? m : rest;
-      if (cnt == 0) continue;
-      const size_t first = uni ? 0 : m;
-      // the odd tail (short last piece / part) of a mostly equal-length batch runs beside the prefix on another
-      // stream of this digest's rotation; a single tail message is itself an "equal-length batch" of one
+    // Launch items: the equal-length prefix (tensor-map kernels), then the remainder.  A remainder of a few LARGE
+    // messages (the short last piece / part, or a handful of whole-file bodies) is launched message by message as
+    // "equal-length batches of one": each gets the TMA path and, for SHA-1 / SHA-256, the schedule-helper warp,
+    // which halves its chain latency compared with the per-lane kernel.  Everything after the first item runs on
+    // further streams of this digest's rotation and is joined before the digests are copied back.
+    struct Item { size_t first, cnt; int kind; };  // kind 0 prefix, 1 lone, 2 ragged
+    std::vector<Item> items;
+    if (m) items.push_back({0, m, 0});
+    if (rest) {
+      bool lone_ok = rest <= 64 && !(d_ok && rest > 1);
+      for (size_t i = m; i < n && lone_ok; i++)
+        lone_ok = msgs[i].length < (1ull << 31) && msgs[i].length >= (rest == 1 ? 1024u : (256u << 10));
+      if (lone_ok) for (size_t i = m; i < n; i++) items.push_back({i, 1, 1});
+      else items.push_back({m, rest, 2});
+    }
+    std::vector<cudaEvent_t> item_joins;
+    for (size_t k = 0; k < items.size() && rc == TH_OK; k++) {
+      const Item& it = items[k];
       cudaStream_t ps = st;
-      if (!uni && m > 0 && !(d_ok && use_order)) {  // (the bitfield memset above is ordered on st only)
+      if (k > 0 && !(it.kind == 2 && d_ok && use_order)) {  // (the bitfield memset above is ordered on st only)
         ps = g.sets[g.next_stream[a]++ % (uint64_t)g.n_sets].alg[a];
         CU(c, cudaStreamWaitEvent(ps, ev_in, 0));
       }
-      const bool lone = !uni && cnt == 1 && msgs[first].length >= 1024;
+      const bool uni = it.kind == 0, lone = it.kind == 1;
+      const size_t first = it.first;
       const uint8_t* pb = uni ? d_uni : (lone ? d_base + msgs[first].offset : d_base);
-      const uint64_t* po = (uni || lone) ? nullptr : d_off;
-      const uint64_t* pl = (uni || lone) ? nullptr : d_len;
-      const uint32_t* pr = (uni || lone) ? nullptr : d_ord;
+      const uint64_t* po = it.kind == 2 ? d_off : nullptr;
+      const uint64_t* pl = it.kind == 2 ? d_len : nullptr;
+      const uint32_t* pr = it.kind == 2 ? d_ord : nullptr;
       const uint64_t pstride = lone ? ((msgs[first].length + 15) & ~15ull) : ustride;
       const uint64_t plen = lone ? msgs[first].length : ulen;
       uint8_t* o = d_out + first * dlen[a];
       if (a == 0)
-        rc = th_sha1_batch(pb, po, pl, pr, pstride, plen, (uint32_t)cnt, o, d_exp ? d_exp + first * 20 : nullptr,
+        rc = th_sha1_batch(pb, po, pl, pr, pstride, plen, (uint32_t)it.cnt, o, d_exp ? d_exp + first * 20 : nullptr,
                            d_ok ? d_ok + first / 32 : nullptr, ps);
       else if (a == 1)
-        rc = th_md5_batch(pb, po, pl, pr, pstride, plen, (uint32_t)cnt, o, ps);
+        rc = th_md5_batch(pb, po, pl, pr, pstride, plen, (uint32_t)it.cnt, o, ps);
       else
-        rc = th_sha256_batch(pb, po, pl, pr, pstride, plen, (uint32_t)cnt, o, ps);
+        rc = th_sha256_batch(pb, po, pl, pr, pstride, plen, (uint32_t)it.cnt, o, ps);
       g.st.launches += 1;
       if (ps != st && rc == TH_OK) {
-        CU(c, cudaEventCreateWithFlags(&ev_rest, cudaEventDisableTiming));
-        CU(c, cudaEventRecord(ev_rest, ps));
+        cudaEvent_t ev;
+        CU(c, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        CU(c, cudaEventRecord(ev, ps));
+        item_joins.push_back(ev);
       }
     }
-    if (ev_rest) {
-      CU(c, cudaStreamWaitEvent(st, ev_rest, 0));
-      CU(c, cudaEventDestroy(ev_rest));
+    for (cudaEvent_t ev : item_joins) {
+      CU(c, cudaStreamWaitEvent(st, ev, 0));
+      CU(c, cudaEventDestroy(ev));
     }
     if (rc != TH_OK) {
       if (rc == TH_ECUDA) return cuda_fail(c, cudaGetLastError(), "digest kernel launch");

@@ -444,3 +444,22 @@ def test_ticket_timing_is_a_consistent_device_timeline(eng):
     assert tm[3] == -1 and tm[4] == -1
     r = eng.result(t, 4, SHA1 | SHA256)
     assert r[SHA1][0].tobytes() == hashlib.sha1(bytes([7]) * ln).digest()
+
+
+def test_few_large_ragged_messages_take_lone_launches(eng):
+    """A handful of large bodies of unlike sizes (whole-file digests of files below the part size): each is launched
+    as an equal-length batch of one (TMA + helper-warp path) on its own stream; with a verify table the SHA-1 goes
+    through the per-lane kernel instead.  Results must not depend on the route."""
+    lens = [300 * 1024 + 5, 1 << 20, 700 * 1024 + 63, (2 << 20) + 1, 256 * 1024, 3 * (1 << 20) + 56]
+    bufs = [oracle.synth(40 + i, n) for i, n in enumerate(lens)]
+    s0 = eng.stats()
+    out = eng.hash_batch(bufs, ALL)
+    s1 = eng.stats()
+    for a in (SHA1, MD5, SHA256):
+        assert (out[a] == ref_digests(a, bufs)).all(), NAMES[a]
+    assert s1["launches"] - s0["launches"] == 3 * len(lens)  # one launch per message and digest
+    exp = ref_digests(SHA1, bufs).copy()
+    exp[2, 0] ^= 1
+    out = eng.hash_batch(bufs, SHA1 | MD5, expected_sha1=exp)
+    assert out["ok"].tolist() == [True, True, False, True, True, True]
+    assert (out[SHA1] == ref_digests(SHA1, bufs)).all() and (out[MD5] == ref_digests(MD5, bufs)).all()
