@@ -484,7 +484,6 @@ struct Assist<Sha256> {
   // ptxas packs into IADD3 — 14 instructions per round instead of 16.
   __device__ static __forceinline__ void rounds(uint32_t* h, const uint4* src, uint32_t one) {
     uint32_t a = h[0], b = h[1], c = h[2], d = h[3], e = h[4], f = h[5], g = h[6], hh = h[7];
-    (void)one;
 #pragma unroll
     for (int q = 0; q < 16; q++) {
       const uint4 v = src[q * 32];
@@ -492,11 +491,16 @@ struct Assist<Sha256> {
 #pragma unroll
       for (int j = 0; j < 4; j++) {
         uint32_t S1 = lop3<LUT_XOR3>(rotr(e, 6), rotr(e, 11), rotr(e, 25));
-        uint32_t t1 = hh + wk[j] + lop3<LUT_CH>(e, f, g);
-        t1 += S1;
+        // hh + wk and d + hh + wk do not depend on this round's inputs: two IMADs off the critical path;
+        // the three adds that do are IADD3s (13 ALU + 2 FMA instructions per round)
+        const uint32_t p = add_fma(hh, wk[j], one);
+        const uint32_t dp = add_fma(d, p, one);
+        const uint32_t ch = lop3<LUT_CH>(e, f, g);
+        const uint32_t t1 = p + ch + S1;
+        const uint32_t en = dp + ch + S1;
         uint32_t S0 = lop3<LUT_XOR3>(rotr(a, 2), rotr(a, 13), rotr(a, 22));
         uint32_t mj = lop3<LUT_MAJ>(a, b, c);
-        hh = g; g = f; f = e; e = d + t1; d = c; c = b; b = a; a = t1 + S0 + mj;
+        hh = g; g = f; f = e; e = en; d = c; c = b; b = a; a = t1 + S0 + mj;
       }
     }
     h[0] += a; h[1] += b; h[2] += c; h[3] += d; h[4] += e; h[5] += f; h[6] += g; h[7] += hh;
@@ -513,10 +517,9 @@ struct Assist<Sha1> {
       if (t >= 16)
         w[t & 15] = rotl(lop3<LUT_XOR3>(w[(t - 3) & 15], w[(t - 8) & 15], w[(t - 14) & 15]) ^ w[t & 15], 1);
       const uint32_t k = t < 20 ? 0x5a827999u : t < 40 ? 0x6ed9eba1u : t < 60 ? 0x8f1bbcdcu : 0xca62c1d6u;
-      o[t & 3] = w[t & 15] + k;
+      o[t & 3] = add_fma(w[t & 15], k, one);  // + K on the FMA pipe (the helper's other work is all ALU; measured neutral)
       if ((t & 3) == 3) sts128(dst + (t >> 2) * 512, o[0], o[1], o[2], o[3]);
     }
-    (void)one;
   }
   __device__ static __forceinline__ void rounds(uint32_t* h, const uint4* src, uint32_t one) {
     uint32_t a = h[0], b = h[1], c = h[2], d = h[3], e = h[4];
