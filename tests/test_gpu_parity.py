@@ -463,3 +463,38 @@ def test_few_large_ragged_messages_take_lone_launches(eng):
     out = eng.hash_batch(bufs, SHA1 | MD5, expected_sha1=exp)
     assert out["ok"].tolist() == [True, True, False, True, True, True]
     assert (out[SHA1] == ref_digests(SHA1, bufs)).all() and (out[MD5] == ref_digests(MD5, bufs)).all()
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3, 4, 5, 6])
+def test_randomised_batches_vs_hashlib(eng, seed):
+    """Differential test over random batch shapes: message counts, length mixes (empty, tiny, block-edge, large),
+    equal-length runs followed by odd tails, random digest masks and corrupted verify tables."""
+    rng = np.random.default_rng(1000 + seed)
+    for _ in range(6):
+        kind = int(rng.integers(0, 4))
+        if kind == 0:      # ragged small
+            lens = rng.integers(0, 3000, int(rng.integers(1, 200))).tolist()
+        elif kind == 1:    # equal-length run + odd tail(s)
+            base = int(rng.choice([1024, 4096, 16384, 65536 + 16, 262144])) + int(rng.integers(0, 2)) * 16
+            lens = [base] * int(rng.integers(1, 150)) + rng.integers(0, base, int(rng.integers(0, 4))).tolist()
+        elif kind == 2:    # block-edge lengths
+            lens = [int(64 * k + d) for k in rng.integers(0, 40, 30) for d in (rng.integers(53, 67),)]
+        else:              # a few large bodies of unlike sizes
+            lens = rng.integers(256 * 1024, 900 * 1024, int(rng.integers(1, 7))).tolist()
+        bufs = [rng.integers(0, 256, int(n), dtype=np.uint8) for n in lens]
+        algs = int(rng.integers(1, 8))
+        exp = None
+        bad = []
+        if algs & SHA1 and rng.integers(0, 2):
+            exp = ref_digests(SHA1, bufs).copy()
+            bad = sorted(set(rng.integers(0, len(lens), int(rng.integers(0, 4))).tolist()))
+            for b in bad:
+                exp[b, int(rng.integers(0, 20))] ^= 1 << int(rng.integers(0, 8))
+        out = eng.hash_batch(bufs, algs, expected_sha1=exp)
+        for a in (SHA1, MD5, SHA256):
+            if algs & a:
+                got, ref = out[a], ref_digests(a, bufs)
+                wrong = np.nonzero((got != ref).any(axis=1))[0]
+                assert wrong.size == 0, (seed, kind, NAMES[a], [lens[i] for i in wrong[:5]])
+        if exp is not None:
+            assert sorted(np.nonzero(~out["ok"])[0].tolist()) == bad, (seed, kind, lens[:8])
