@@ -188,6 +188,8 @@ def main():
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--e2e-slots", type=int, default=8)
     ap.add_argument("--e2e-gib", type=int, default=16, help="cap on the pinned bytes the e2e leg cycles through per GPU")
+    ap.add_argument("--e2e-device-mult", type=int, default=0,
+                    help="device staging ring = this many pinned rings (0: 1 for pieces, 3 for 16 MiB parts, whose chains outlast the copy)")
     ap.add_argument("--staging", default="", help="override bulk staging geometry, e.g. 512x2 (tuning only)")
     ap.add_argument("--path", type=int, default=0, help="0 auto, 1 bulk, 2 tile, 3 sliced (tuning only)")
     args = ap.parse_args()
@@ -308,7 +310,8 @@ def main():
         while per_slot > 32 and slots * per_slot * ln > budget:
             per_slot //= 2
         slot_bytes = per_slot * ln
-        eng = Engine([local], ring_bytes=slots * slot_bytes)
+        dev_mult = args.e2e_device_mult or (1 if algs == "sha1" else 3)
+        eng = Engine([local], ring_bytes=slots * slot_bytes, device_bytes=dev_mult * slots * slot_bytes)
         mask = ALG_SHA1 if algs == "sha1" else (ALG_MD5 | ALG_SHA256)
         offs_s = np.arange(per_slot, dtype=np.uint64) * ln
         lens_s = np.full(per_slot, ln, np.uint64)
@@ -323,12 +326,10 @@ def main():
         for sid in held:
             eng.ring_release(sid)
 
-        def e2e_step():
-            tickets = []
-            for k in range(slots):
-                sid, _ = eng.ring_acquire(slot_bytes)
-                exp_k = exp_host[k * per_slot:(k + 1) * per_slot] if exp_host is not None else None
-                tickets.append(eng.submit(sid, offs_s, lens_s, mask, exp_k))
+        # A stream of batches, as the files loop of lib/upload.js is: step s submits its slots, then collects
+        # the digests of step s-1 (whose chains ran under this step's copies); the last step's are collected
+        # before the clock stops, so every step's H2D and D2H lie inside the timed region.
+        def collect(tickets):
             res = [eng.result(t, per_slot, mask, want_ok=exp_host is not None) for t in tickets]
             if dist is not None:  # digests are gathered on the host; no GPU collective
                 mine = torch.from_numpy(np.concatenate([r[ALG_SHA1 if algs == "sha1" else ALG_MD5] for r in res]))
@@ -336,14 +337,25 @@ def main():
                 dist.gather(mine, gl, dst=0)
             return res
 
-        for _ in range(max(1, min(args.warmup, 2))):
-            res = e2e_step()
+        def e2e_run(nsteps):
+            prev, res = None, None
+            for _ in range(nsteps):
+                tickets = []
+                for k in range(slots):
+                    sid, _ = eng.ring_acquire(slot_bytes)
+                    exp_k = exp_host[k * per_slot:(k + 1) * per_slot] if exp_host is not None else None
+                    tickets.append(eng.submit(sid, offs_s, lens_s, mask, exp_k))
+                if prev is not None:
+                    res = collect(prev)
+                prev = tickets
+            return collect(prev)
+
+        res = e2e_run(max(1, min(args.warmup, 2)))
         s0 = eng.stats()
         barrier()
         w0 = time.perf_counter()
         e2e_steps = max(1, min(args.steps, 5))
-        for _ in range(e2e_steps):
-            res = e2e_step()
+        res = e2e_run(e2e_steps)
         barrier()
         w1 = time.perf_counter()
         s1 = eng.stats()
@@ -363,7 +375,8 @@ def main():
         e2e = {"value": round(world * slots * slot_bytes / dt / GB, 3), "unit": "GB/s",
                "h2d_bytes_per_step": int((s1["h2d_bytes"] - s0["h2d_bytes"]) // e2e_steps),
                "d2h_bytes_per_step": int((s1["d2h_bytes"] - s0["d2h_bytes"]) // e2e_steps),
-               "messages_per_gpu": slots * per_slot, "steps": e2e_steps, "ms_per_step": round(dt * 1e3, 3), "timing": "host wall clock around submit..result, max over ranks",
+               "messages_per_gpu": slots * per_slot, "steps": e2e_steps, "ms_per_step": round(dt * 1e3, 3), "timing": "host wall clock around %d streamed steps (submit all slots, collect the previous step's digests; last step drained inside), max over ranks" % e2e_steps,
+               "pinned_ring_bytes": slots * slot_bytes, "device_ring_bytes": dev_mult * slots * slot_bytes,
                "launches_per_step": int((s1["launches"] - s0["launches"]) // e2e_steps),
                "kernel_ms_per_step": round((s1["kernel_ms"] - s0["kernel_ms"]) / e2e_steps, 3)}
         eng.close()

@@ -68,6 +68,7 @@ def lib() -> C.CDLL:
     L = C.CDLL(_LIB)
     vp, u64, u32, i32 = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int
     L.th_init.argtypes = [C.POINTER(i32), i32, C.c_size_t, C.POINTER(vp)]
+    L.th_init_staged.argtypes = [C.POINTER(i32), i32, C.c_size_t, C.c_size_t, C.POINTER(vp)]
     L.th_shutdown.argtypes = [vp]
     L.th_gpu_count.argtypes = [vp]
     L.th_ring_acquire.argtypes = [vp, i32, C.c_size_t, C.POINTER(vp), C.POINTER(u64)]

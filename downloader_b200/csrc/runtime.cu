@@ -56,10 +56,12 @@ struct JobBuf {
 struct Slot {
   uint64_t id = 0;
   int gpu = 0;
-  size_t off = 0, bytes = 0;   // region of the ring
+  size_t off = 0, bytes = 0;   // region of the pinned ring
+  size_t doff = 0;             // region of the device ring (same length)
   size_t used = 0;             // bytes the caller asked for (what the H2D copy moves)
   bool submitted = false;
-  bool done = false;           // every ticket completed (or slot released) -> region reusable
+  bool host_free = false;      // H2D copy completed (or slot released) -> pinned region reusable
+  bool done = false;           // every ticket completed (or slot released) -> device region reusable
   std::vector<uint64_t> tickets;  // a slot may be submitted several times (pieces AND parts of the same bytes)
   cudaEvent_t ev_copied = nullptr;  // H2D of the slot, issued by its first submit
 };
@@ -87,7 +89,8 @@ struct Ticket {
 // Kernels of different submits must be able to overlap: a slot of large parts holds only a few message
 // groups, and a chain's latency (0.26 s for a 16 MiB SHA-256 part) is far longer than the slot's H2D copy.
 // Tickets therefore rotate over a pool of stream sets; only the H2D copies share one stream (one PCIe link).
-constexpr int kStreamSets = 10;
+constexpr int kStreamSets = 10;      // default
+constexpr int kMaxStreamSets = 40;   // TRITONHASH_STREAM_SETS may ask for more (streams then alias on the 32 queues)
 // 10 sets x 3 digest streams + copy + misc = 32 streams: exactly the 32 hardware work queues a process can ask
 // for (CUDA_DEVICE_MAX_CONNECTIONS, set in th_init when CUDA is not initialised yet).  With the default of 8
 // queues streams alias, and a D2H copy queued behind a 0.26 s kernel stalls unrelated kernels in its queue.
@@ -99,14 +102,19 @@ struct Gpu {
   int dev = -1;
   cudaStream_t s_copy = nullptr, s_misc = nullptr;  // H2D copies; synchronous odd jobs (ETag combine)
   cudaEvent_t ev_epoch = nullptr;                   // recorded in th_init: origin of th_ticket_timing
-  StreamSet sets[kStreamSets];
-  int n_sets = kStreamSets;     // TRITONHASH_STREAM_SETS (1..10) narrows the rotation
+  StreamSet sets[kMaxStreamSets];
+  int n_sets = kStreamSets;     // TRITONHASH_STREAM_SETS (1..40) overrides
   uint64_t next_stream[3] = {0, 0, 0};  // each digest rotates over its own 10 streams, whatever mix of submits arrives
+  // Two FIFO rings with separate lifetimes: a slot's pinned bytes are needed only until its H2D copy has run,
+  // its device bytes until the last kernel reading them has finished.  A chain over a 16 MiB part runs for
+  // ~0.25 s, several times longer than the copy of the whole slot, so the device ring may be made (much) larger
+  // than the pinned one (th_init_staged): HBM, not pinned host memory, holds the bytes in flight.
   uint8_t* ring_h = nullptr;
   uint8_t* ring_d = nullptr;
-  size_t ring_bytes = 0;
-  size_t head = 0, tail = 0;   // ring allocator: live region is [head, tail) modulo wrap
-  std::deque<Slot> slots;      // FIFO, oldest first
+  size_t ring_bytes = 0, dring_bytes = 0;
+  size_t head = 0, tail = 0;   // pinned ring allocator: live region is [head, tail) modulo wrap
+  size_t dhead = 0, dtail = 0; // device ring allocator, same scheme
+  std::deque<Slot> slots;      // FIFO, oldest first; a slot leaves when its device region is free
   std::vector<JobBuf*> free_jobs;
   // Staging arena: one pinned + one device block allocated in th_init, carved first-fit into job buffers.
   // cudaMalloc / cudaHostAlloc on the submit path would wait for every running kernel (they synchronise the
@@ -189,7 +197,27 @@ JobBuf* get_job(th_ctx* c, Gpu& g, size_t n, int* rc) {
   return jb;
 }
 
-// Marks finished tickets' slots reusable and advances the ring head over them.
+// Oldest slot (in acquisition order) whose pinned bytes are still needed; nullptr when the pinned ring is idle.
+Slot* oldest_host_busy(Gpu& g) {
+  for (auto& s : g.slots)
+    if (!s.host_free) return &s;
+  return nullptr;
+}
+
+// Where `need` bytes fit at the tail of a FIFO ring whose live region is [head, tail) modulo one wrap;
+// (size_t)-1 when they do not.
+size_t ring_fit(size_t cap, size_t head, size_t tail, bool idle, size_t need) {
+  if (idle) return 0;
+  if (tail > head) {                       // live region does not wrap
+    if (cap - tail >= need) return tail;
+    if (head >= need) return 0;
+  } else if (tail < head) {                // wrapped: the free gap is [tail, head)
+    if (head - tail >= need) return tail;
+  }
+  return (size_t)-1;
+}
+
+// Marks copied slots' pinned bytes and finished slots' device bytes reusable and advances both ring heads.
 void reap(th_ctx* c, Gpu& g, bool block_on_oldest) {
   for (auto& s : g.slots) {
     if (s.done || !s.submitted) continue;
@@ -206,14 +234,18 @@ void reap(th_ctx* c, Gpu& g, bool block_on_oldest) {
       }
       all &= t->finished;
     }
-    if (all) s.done = true;
+    if (all) s.done = s.host_free = true;
+    if (!s.host_free && s.ev_copied && cudaEventQuery(s.ev_copied) == cudaSuccess) s.host_free = true;
   }
   while (!g.slots.empty() && g.slots.front().done) {
     if (g.slots.front().ev_copied) cudaEventDestroy(g.slots.front().ev_copied);
     g.slots.pop_front();
-    g.head = g.slots.empty() ? g.tail : g.slots.front().off;
+    g.dhead = g.slots.empty() ? g.dtail : g.slots.front().doff;
   }
-  if (g.slots.empty()) g.head = g.tail = 0;
+  if (g.slots.empty()) g.dhead = g.dtail = 0;
+  const Slot* busy = oldest_host_busy(g);
+  if (busy) g.head = busy->off;
+  else g.head = g.tail = 0;
 }
 
 void CUDART_CB host_done(void* p) {
@@ -258,7 +290,7 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
   CU(c, cudaSetDevice(g.dev));
   // H2D: payload (the whole ring slot, once — later submits on the same slot reuse it) then descriptors.
   if (slot && !slot->ev_copied) {
-    CU(c, cudaMemcpyAsync(g.ring_d + slot->off, g.ring_h + slot->off, slot->used, cudaMemcpyHostToDevice, g.s_copy));
+    CU(c, cudaMemcpyAsync(g.ring_d + slot->doff, g.ring_h + slot->off, slot->used, cudaMemcpyHostToDevice, g.s_copy));
     g.st.h2d_bytes += slot->used;
     CU(c, cudaEventCreateWithFlags(&slot->ev_copied, cudaEventDisableTiming));
     CU(c, cudaEventRecord(slot->ev_copied, g.s_copy));
@@ -409,7 +441,13 @@ void free_ticket_events(Ticket* t) {
 extern "C" {
 
 int th_init(const int* gpu_ids, int n_gpus, size_t ring_bytes_per_gpu, th_ctx** out) {
+  return th_init_staged(gpu_ids, n_gpus, ring_bytes_per_gpu, 0, out);
+}
+
+int th_init_staged(const int* gpu_ids, int n_gpus, size_t ring_bytes_per_gpu, size_t device_bytes_per_gpu, th_ctx** out) {
   if (!out || n_gpus <= 0) return TH_EINVAL;
+  if (device_bytes_per_gpu == 0) device_bytes_per_gpu = ring_bytes_per_gpu;
+  if (ring_bytes_per_gpu == 0) device_bytes_per_gpu = 0;
   *out = nullptr;
   setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);  // read when the CUDA context is created; no effect if it already exists
   int count = 0;
@@ -421,7 +459,7 @@ int th_init(const int* gpu_ids, int n_gpus, size_t ring_bytes_per_gpu, th_ctx** 
     g.dev = gpu_ids ? gpu_ids[i] : i;
     if (const char* e = getenv("TRITONHASH_STREAM_SETS")) {
       const int v = atoi(e);
-      if (v >= 1 && v <= kStreamSets) g.n_sets = v;
+      if (v >= 1 && v <= kMaxStreamSets) g.n_sets = v;
     }
     cudaDeviceProp prop{};
     if (g.dev < 0 || g.dev >= count || cudaGetDeviceProperties(&prop, g.dev) != cudaSuccess || prop.major < 10) {
@@ -438,10 +476,11 @@ int th_init(const int* gpu_ids, int n_gpus, size_t ring_bytes_per_gpu, th_ctx** 
     if (e == cudaSuccess && ring_bytes_per_gpu) {
       g.ring_bytes = align_up(ring_bytes_per_gpu, kRingAlign);
       e = cudaHostAlloc((void**)&g.ring_h, g.ring_bytes, cudaHostAllocPortable);
-      if (e == cudaSuccess) e = cudaMalloc((void**)&g.ring_d, g.ring_bytes);
+      g.dring_bytes = align_up(device_bytes_per_gpu, kRingAlign);
+      if (e == cudaSuccess) e = cudaMalloc((void**)&g.ring_d, g.dring_bytes);
     }
     if (e == cudaSuccess) {  // ~108 bytes of descriptors + digests per message; 1/128 of the ring covers 16 KiB messages
-      g.arena_bytes = align_up(std::max<size_t>(64u << 20, g.ring_bytes / 128), 256);
+      g.arena_bytes = align_up(std::max<size_t>(64u << 20, std::max(g.ring_bytes, g.dring_bytes) / 128), 256);
       e = cudaHostAlloc((void**)&g.arena_h, g.arena_bytes, cudaHostAllocPortable);
       if (e == cudaSuccess) e = cudaMalloc((void**)&g.arena_d, g.arena_bytes);
       if (e == cudaSuccess) g.arena_free[0] = g.arena_bytes;
@@ -491,34 +530,38 @@ int th_ring_acquire(th_ctx* c, int gpu, size_t bytes, void** host_ptr, th_slot* 
   if (c->sticky) return c->sticky;
   Gpu& g = c->gpus[(size_t)gpu];
   const size_t need = align_up(bytes, kRingAlign);
-  if (need > g.ring_bytes) return TH_ETOOBIG;
+  if (need > g.ring_bytes || need > g.dring_bytes) return TH_ETOOBIG;
   cudaSetDevice(g.dev);
   for (;;) {
     reap(c, g, false);
-    size_t off = (size_t)-1;
-    if (g.slots.empty()) {
-      off = 0;
-    } else if (g.tail >= g.head && g.tail != g.head) {  // live region does not wrap
-      if (g.ring_bytes - g.tail >= need) off = g.tail;
-      else if (g.head >= need) off = 0;
-    } else if (g.tail < g.head) {                       // wrapped: free gap is [tail, head)
-      if (g.head - g.tail >= need) off = g.tail;
-    }
-    if (off != (size_t)-1) {
+    Slot* busy = oldest_host_busy(g);
+    const size_t off = ring_fit(g.ring_bytes, g.head, g.tail, busy == nullptr, need);
+    const size_t doff = ring_fit(g.dring_bytes, g.dhead, g.dtail, g.slots.empty(), need);
+    if (off != (size_t)-1 && doff != (size_t)-1) {
       Slot s;
       s.id = c->next_id++;
       s.gpu = gpu;
       s.off = off;
+      s.doff = doff;
       s.bytes = need;
       s.used = (bytes + 15) & ~(size_t)15;
-      if (g.slots.empty()) g.head = off;
+      if (!busy) g.head = off;
       g.tail = off + need;
+      if (g.slots.empty()) g.dhead = doff;
+      g.dtail = doff + need;
       g.slots.push_back(s);
       *host_ptr = g.ring_h + off;
       *slot = s.id;
       return TH_OK;
     }
-    // full: wait for the oldest slot's ticket
+    if (off == (size_t)-1) {  // pinned ring full: wait for the oldest outstanding H2D copy
+      if (!busy->submitted) return TH_EBUSY;
+      cudaError_t e = cudaEventSynchronize(busy->ev_copied);
+      if (e != cudaSuccess) return cuda_fail(c, e, "cudaEventSynchronize(slot copy)");
+      busy->host_free = true;
+      continue;
+    }
+    // device ring full: wait for the oldest slot's tickets
     if (!g.slots.front().submitted) return TH_EBUSY;
     reap(c, g, true);
     if (c->sticky) return c->sticky;
@@ -532,7 +575,7 @@ int th_ring_release(th_ctx* c, th_slot slot) {
     for (auto& s : g.slots)
       if (s.id == slot) {
         if (s.submitted) return TH_ESTATE;
-        s.done = true;
+        s.done = s.host_free = true;
         reap(c, g, false);
         return TH_OK;
       }
@@ -556,7 +599,7 @@ static int submit_common(th_ctx* c, int gpu, Slot* slot, const void* d_base_user
   t->cb = cb;
   t->user = user;
   t->ctx = c;
-  const uint8_t* d_base = slot ? g.ring_d + slot->off : static_cast<const uint8_t*>(d_base_user);
+  const uint8_t* d_base = slot ? g.ring_d + slot->doff : static_cast<const uint8_t*>(d_base_user);
   if (slot) t->slot_id = slot->id;
   rc = enqueue(c, g, t, d_base, slot, msgs, n, mask, t->has_expected ? expected : nullptr);
   if (rc != TH_OK) {

@@ -73,13 +73,23 @@ typedef void (*th_done_cb)(void* user, th_ticket ticket, int status);
  * ring + its device mirror, the copy / compute streams and the descriptor staging buffers.
  * gpu_ids == NULL -> devices 0..n_gpus-1.  ring_bytes_per_gpu may be 0 (device-resident use only). */
 int th_init(const int* gpu_ids, int n_gpus, size_t ring_bytes_per_gpu, th_ctx** out);
+/* Same, with the device-side staging ring sized separately (0 = same as the pinned ring, which is th_init).
+ * A slot's pinned bytes are reusable as soon as its H2D copy has run; its device bytes only when the last
+ * kernel reading them has finished.  The digest chain of one 16 MiB part runs for ~0.25 s — several times
+ * longer than the copy of a whole slot — so to keep PCIe busy with large parts the bytes in flight
+ * (≈ 55 GB/s x chain latency) must fit the DEVICE ring; the pinned ring only needs two or three slots.
+ * No counterpart in the reference (Node's Buffers are plain heap memory). */
+int th_init_staged(const int* gpu_ids, int n_gpus, size_t ring_bytes_per_gpu, size_t device_bytes_per_gpu,
+                   th_ctx** out);
 int th_shutdown(th_ctx* ctx);
 int th_gpu_count(const th_ctx* ctx);
 
 /* ---- host path: pinned ring -> H2D -> digest kernels -> D2H digests -------------------------
  * th_ring_acquire hands out `bytes` of pinned host memory the caller fills (fs.read target —
- * replaces the GC-owned piece/part Buffers of [dep] webtorrent / minio).  Blocks while the ring is
- * full of in-flight slots; the slot returns to the ring when its ticket completes. */
+ * replaces the GC-owned piece/part Buffers of [dep] webtorrent / minio).  Blocks while the pinned ring
+ * is full of slots whose H2D copy has not run yet, or the device ring is full of slots whose tickets have not
+ * completed (TH_EBUSY instead if the slot it would wait for has not been submitted).  The pinned bytes return
+ * to the ring when the slot's copy completes, the device bytes when all of its tickets have. */
 int th_ring_acquire(th_ctx* ctx, int gpu, size_t bytes, void** host_ptr, th_slot* slot);
 /* Drops a slot that was acquired but will not be submitted. */
 int th_ring_release(th_ctx* ctx, th_slot slot);
@@ -87,7 +97,8 @@ int th_ring_release(th_ctx* ctx, th_slot slot);
 /* Non-blocking.  Hashes msgs[0..n) of the slot with every digest in alg_mask.
  * A slot may be submitted more than once while one of its tickets is still outstanding — e.g. once as
  * torrent pieces (SHA-1) and once as S3 parts (MD5 | SHA-256) of the same bytes: the slot crosses PCIe
- * once, with its first submit, and returns to the ring when all of its tickets have completed.
+ * once, with its first submit; the slot id stays valid for further submits until all of its tickets have completed
+ * (host_ptr must not be written after the first submit).
  * expected_sha1 (nullable, n*20 raw bytes = info.pieces of the .torrent, [dep] parse-torrent@7.0.0)
  * enables the fused compare: bit i of ok_bits = (sha1(msg i) == expected i), which is webtorrent's
  * `hash === this._hashes[index]` -> bitfield.set(index) ([dep] lib/torrent.js). */

@@ -98,8 +98,8 @@ bool read_msgs(napi_env env, napi_value arr, std::vector<th_msg>* out) {
 
 // init(gpuIds: number[], ringBytesPerGpu: number)
 napi_value Init(napi_env env, napi_callback_info info) {
-  size_t argc = 2;
-  napi_value argv[2];
+  size_t argc = 3;  // init(gpuIds, pinnedRingBytes[, deviceRingBytes])
+  napi_value argv[3];
   NAPI_OK(napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr));
   uint32_t n = 0;
   NAPI_OK(napi_get_array_length(env, argv[0], &n));
@@ -111,7 +111,9 @@ napi_value Init(napi_env env, napi_callback_info info) {
   }
   double ring = 0;
   NAPI_OK(napi_get_value_double(env, argv[1], &ring));
-  int rc = th_init(ids.data(), static_cast<int>(n), static_cast<size_t>(ring), &g_ctx);
+  double dring = 0;  // 0 = same as the pinned ring
+  if (argc > 2) NAPI_OK(napi_get_value_double(env, argv[2], &dring));
+  int rc = th_init_staged(ids.data(), static_cast<int>(n), static_cast<size_t>(ring), static_cast<size_t>(dring), &g_ctx);
   if (rc != TH_OK) return throw_th(env, rc, "init");  // TH_ENODEVICE: there is no CPU fallback
   napi_value u;
   napi_get_undefined(env, &u);

@@ -15,9 +15,10 @@ const SHA256 = addon.SHA256
 
 let started = false
 
-function init (gpuIds = [0], ringBytesPerGpu = 1 << 30) {
+// deviceBytesPerGpu (0 = same as the pinned ring) sizes the device staging ring: th_init_staged
+function init (gpuIds = [0], ringBytesPerGpu = 1 << 30, deviceBytesPerGpu = 0) {
   if (!started) {
-    addon.init(gpuIds, ringBytesPerGpu) // throws when no sm_100 GPU: there is no CPU fallback
+    addon.init(gpuIds, ringBytesPerGpu, deviceBytesPerGpu) // throws when no sm_100 GPU: there is no CPU fallback
     started = true
   }
 }

@@ -498,3 +498,67 @@ def test_randomised_batches_vs_hashlib(eng, seed):
                 assert wrong.size == 0, (seed, kind, NAMES[a], [lens[i] for i in wrong[:5]])
         if exp is not None:
             assert sorted(np.nonzero(~out["ok"])[0].tolist()) == bad, (seed, kind, lens[:8])
+
+
+def test_small_pinned_ring_large_device_ring(torch):
+    """th_init_staged: pinned bytes are reusable once copied, device bytes once hashed.  48 slots of unlike,
+    odd sizes stream through a 3 MiB pinned ring backed by a 64 MiB device ring with no result read until the
+    end; each slot's pinned bytes are overwritten by later slots long before its digests are collected."""
+    from downloader_b200 import Engine
+    rng = np.random.default_rng(77)
+    with Engine([0], ring_bytes=3 << 20, device_bytes=64 << 20) as e:
+        assert e.device_bytes == 64 << 20
+        jobs = []
+        for k in range(48):
+            nbytes = int(rng.integers(1, 1 << 20))
+            slot, view = e.ring_acquire(nbytes)
+            data = oracle.synth(1000 + k, nbytes)
+            view[:] = data
+            unit = int(rng.choice([4096, 65536, 100000]))
+            offs = np.arange(0, nbytes, unit, dtype=np.uint64)
+            lens = np.minimum(unit, nbytes - offs).astype(np.uint64)
+            t1 = e.submit(slot, offs, lens, SHA1)
+            t2 = e.submit(slot, offs, lens, MD5 | SHA256)  # same slot again: no second copy
+            jobs.append((data, offs, lens, t1, t2))
+        st = e.stats()
+        assert st["h2d_bytes"] < sum(j[0].size for j in jobs) + 48 * 2 * (1 << 16)  # one payload copy per slot
+        for data, offs, lens, t1, t2 in jobs:
+            bufs = [data[int(o):int(o + l)] for o, l in zip(offs, lens)]
+            r1 = e.result(t1, offs.size, SHA1)
+            r2 = e.result(t2, offs.size, MD5 | SHA256)
+            assert (r1[SHA1] == ref_digests(SHA1, bufs)).all()
+            assert (r2[MD5] == ref_digests(MD5, bufs)).all()
+            assert (r2[SHA256] == ref_digests(SHA256, bufs)).all()
+
+
+def test_device_ring_smaller_than_the_stream_blocks_and_recovers(torch):
+    """Device ring of two slots: the third acquire waits for the oldest slot's tickets; an unsubmitted oldest
+    slot makes it TH_EBUSY instead of a deadlock; oversize requests are TH_ETOOBIG for either ring."""
+    from downloader_b200 import Engine
+    from downloader_b200 import TritonHashError
+    ln = 1 << 20
+    offs = np.arange(0, ln, 1 << 18, dtype=np.uint64)
+    lens = np.full(offs.size, 1 << 18, np.uint64)
+    with Engine([0], ring_bytes=4 << 20, device_bytes=2 << 20) as e:
+        with pytest.raises(TritonHashError) as ei:
+            e.ring_acquire(3 << 20)  # fits the pinned ring, not the device ring
+        assert ei.value.code == -7
+        out = []
+        for k in range(6):
+            slot, view = e.ring_acquire(ln)
+            view[:] = oracle.synth(50 + k, ln)
+            out.append((k, e.submit(slot, offs, lens, SHA256)))
+        for k, t in out:
+            data = oracle.synth(50 + k, ln)
+            assert (e.result(t, 4, SHA256)[SHA256] == ref_digests(SHA256, [data[i << 18:(i + 1) << 18] for i in range(4)])).all()
+        a, _ = e.ring_acquire(ln)
+        b, vb = e.ring_acquire(ln)
+        with pytest.raises(TritonHashError) as ei:
+            e.ring_acquire(ln)  # device ring full and slot `a` was never submitted
+        assert ei.value.code == -6
+        e.ring_release(a)
+        vb[:] = 7
+        t = e.submit(b, offs, lens, MD5)
+        c, _ = e.ring_acquire(ln)  # fits again
+        e.ring_release(c)
+        assert (e.result(t, 4, MD5)[MD5] == ref_digests(MD5, [np.full(1 << 18, 7, np.uint8)] * 4)).all()
