@@ -50,7 +50,6 @@ struct JobBuf {
   size_t o_md5(size_t n) const { return o_sha1(n) + align_up(n * 20, 256); }
   size_t o_sha256(size_t n) const { return o_md5(n) + align_up(n * 16, 256); }
   size_t o_ok(size_t n) const { return o_sha256(n) + align_up(n * 32, 256); }
-  size_t o_end(size_t n) const { return o_ok(n) + align_up(((n + 31) / 32) * 4, 256); }
 };
 
 struct Slot {

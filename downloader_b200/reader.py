@@ -68,6 +68,14 @@ class _ConcatFiles:
         self._fds.clear()
 
 
+def _slots_in_flight(engine, batch_bytes: int, in_flight: Optional[int]) -> int:
+    """How many submitted slots to leave uncollected: as many as the device staging ring holds (a chain over a
+    large part runs for much longer than its slot's copy; th_ring_acquire does the waiting when a ring fills)."""
+    if in_flight is not None:
+        return max(1, in_flight)
+    return max(2, int(getattr(engine, "device_bytes", 0)) // max(batch_bytes, 1) - 1)
+
+
 def _stream_messages(engine, src: _ConcatFiles, bounds: Sequence[Tuple[int, int]], algs: int,
                      expected_sha1: Optional[np.ndarray], gpu: int, batch_bytes: int, in_flight: int) -> dict:
     """Hashes messages given as [start,end) ranges of the concatenated stream (ascending, non-overlapping)."""
@@ -75,6 +83,7 @@ def _stream_messages(engine, src: _ConcatFiles, bounds: Sequence[Tuple[int, int]
     out = {a: np.zeros((n, DIGEST_LEN[a]), np.uint8) for a in (ALG_SHA1, ALG_MD5, ALG_SHA256) if algs & a}
     ok = np.zeros(n, bool) if expected_sha1 is not None else None
     pending: List[Tuple[int, int, int]] = []  # (ticket, first message, count)
+    in_flight = _slots_in_flight(engine, batch_bytes, in_flight)
 
     def drain(k: int) -> None:
         while len(pending) > k:
@@ -116,7 +125,7 @@ def _stream_messages(engine, src: _ConcatFiles, bounds: Sequence[Tuple[int, int]
 
 
 def hash_file_parts(engine, path: str, ranges: Sequence[Tuple[int, int]], algs: int = ALG_MD5 | ALG_SHA256, gpu: int = 0,
-                    batch_bytes: int = 256 << 20, in_flight: int = 2) -> dict:
+                    batch_bytes: int = 256 << 20, in_flight: Optional[int] = None) -> dict:
     """Per-part digests of one file (minio's first pass over every part, all parts in a few launches)."""
     size = os.path.getsize(path)
     src = _ConcatFiles([(path, size)])
@@ -132,7 +141,7 @@ def piece_bounds(total: int, piece_length: int) -> List[Tuple[int, int]]:
 
 
 def verify_pieces(engine, files: Sequence[Tuple[str, int]], piece_length: int, expected_sha1, gpu: int = 0,
-                  batch_bytes: int = 256 << 20, in_flight: int = 2) -> dict:
+                  batch_bytes: int = 256 << 20, in_flight: Optional[int] = None) -> dict:
     """Bulk re-verify of an on-disk download ([dep] webtorrent `_verifyPieces`): returns {'ok': bool[n]
     (the bitfield), ALG_SHA1: digests}.  Missing files hash as zeros and simply fail verification."""
     src = _ConcatFiles(files)
@@ -147,7 +156,7 @@ def verify_pieces(engine, files: Sequence[Tuple[str, int]], piece_length: int, e
 
 
 def hash_media_file(engine, path: str, piece_length: int, expected_sha1, part_ranges: Sequence[Tuple[int, int]],
-                    part_algs: int = ALG_MD5 | ALG_SHA256, gpu: int = 0, batch_bytes: int = 512 << 20, in_flight: int = 2) -> dict:
+                    part_algs: int = ALG_MD5 | ALG_SHA256, gpu: int = 0, batch_bytes: int = 512 << 20, in_flight: Optional[int] = None) -> dict:
     """One pass over a staged media file feeding BOTH consumers of its bytes: SHA-1 by torrent piece (with
     the fused verify) and MD5 / SHA-256 by S3 part.  Each ring slot is read once, crosses PCIe once, and is
     submitted twice (th_submit allows that).  Slots hold whole parts, and parts are multiples of the piece
@@ -162,6 +171,7 @@ def hash_media_file(engine, path: str, piece_length: int, expected_sha1, part_ra
     parts = {a: np.zeros((len(part_ranges), DIGEST_LEN[a]), np.uint8) for a in (ALG_MD5, ALG_SHA256) if part_algs & a}
     src = _ConcatFiles([(path, size)])
     pending: List[tuple] = []
+    in_flight = _slots_in_flight(engine, batch_bytes, in_flight)
 
     def drain(k):
         while len(pending) > k:
