@@ -403,6 +403,9 @@ def main():
         "hbm": {"achieved": round(per_gpu, 2), "peak": hbm_peak, "frac": round(per_gpu / hbm_peak, 4), "source": peak_src},
         "algorithmic_bytes_per_launch": total_bytes,
         "parallelism_ceiling": round(min(1.0, warps / (592.0 * w_sat)), 4),
+        "note": "frac can exceed 1: SURVEY 8d's bound counts every op on the 64-lane/clk/SM alu pipe, and the kernels issue "
+                "the plain adds as IMAD on the fma pipe (ncu: alu pipe ~90 % busy at this rate, profiles/r1_*_ncu_summary.txt); "
+                "below parallelism_ceiling < 1 the batch is chain-latency-bound, not pipe-bound",
     }
 
     line = {
