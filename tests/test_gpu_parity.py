@@ -562,3 +562,45 @@ def test_device_ring_smaller_than_the_stream_blocks_and_recovers(torch):
         c, _ = e.ring_acquire(ln)  # fits again
         e.ring_release(c)
         assert (e.result(t, 4, MD5)[MD5] == ref_digests(MD5, [np.full(1 << 18, 7, np.uint8)] * 4)).all()
+
+
+def test_one_context_many_caller_threads(torch):
+    """th_* on one context are serialised by the library (tritonhash.h, threading): four caller threads acquire,
+    fill, submit and collect on the same context at once; every digest must match hashlib."""
+    import threading
+    from downloader_b200 import Engine
+    errors = []
+    with Engine([0], ring_bytes=8 << 20, device_bytes=64 << 20) as e:
+        def worker(tid):
+            try:
+                rng = np.random.default_rng(500 + tid)
+                for it in range(12):
+                    nbytes = int(rng.integers(16, 512 << 10))
+                    unit = int(rng.choice([1024, 16384, 65536]))
+                    data = rng.integers(0, 256, nbytes, dtype=np.uint8)
+                    while True:
+                        try:
+                            slot, view = e.ring_acquire(nbytes)
+                            break
+                        except Exception as ex:  # TH_EBUSY: the oldest slot belongs to a thread that has not submitted yet
+                            if getattr(ex, "code", 0) != -6:
+                                raise
+                    view[:] = data
+                    offs = np.arange(0, nbytes, unit, dtype=np.uint64)
+                    lens = np.minimum(unit, nbytes - offs).astype(np.uint64)
+                    algs = int(rng.integers(1, 8))
+                    t = e.submit(slot, offs, lens, algs)
+                    r = e.result(t, offs.size, algs)
+                    bufs = [data[int(o):int(o + l)] for o, l in zip(offs, lens)]
+                    for a in (SHA1, MD5, SHA256):
+                        if algs & a and not (r[a] == ref_digests(a, bufs)).all():
+                            errors.append((tid, it, NAMES[a]))
+            except Exception as ex:  # noqa: BLE001
+                errors.append((tid, repr(ex)))
+        th = [threading.Thread(target=worker, args=(i,)) for i in range(4)]
+        for x in th:
+            x.start()
+        for x in th:
+            x.join()
+        assert not errors, errors[:4]
+        assert e.stats()["submits"] == 48
