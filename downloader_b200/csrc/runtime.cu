@@ -334,13 +334,33 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
     // further streams of this digest's rotation and is joined before the digests are copied back.
     struct Item { size_t first, cnt; int kind; };  // kind 0 prefix, 1 lone, 2 ragged
     std::vector<Item> items;
+    size_t ragged_skip = 0;  // leading entries of the order that are launched alone
     if (m) items.push_back({0, m, 0});
     if (rest) {
       bool lone_ok = rest <= 64 && !(d_ok && rest > 1);
       for (size_t i = m; i < n && lone_ok; i++)
         lone_ok = msgs[i].length < (1ull << 31) && msgs[i].length >= (rest == 1 ? 1024u : (256u << 10));
-      if (lone_ok) for (size_t i = m; i < n; i++) items.push_back({i, 1, 1});
-      else items.push_back({m, rest, 2});
+      if (lone_ok) {
+        for (size_t i = m; i < n; i++) items.push_back({i, 1, 1});
+      } else {
+        // Heavy-tailed remainders: the batch cannot finish before its longest message's chain does, and that chain
+        // runs about twice as fast through the TMA / helper-warp path as in a lane of the per-lane kernel.  The
+        // few outliers (>= 256 KiB and >= 8 x the median; they lead the descending order; at most 8) are peeled into lone
+        // launches; the per-lane launch takes the rest of the order.
+        size_t peel = 0;
+        if (use_order && !d_ok) {
+          const uint64_t median = h_len[m + h_ord[m + rest / 2]];
+          const size_t peel_max = (size_t)std::max(1, g.n_sets - 2);  // each lone launch wants a stream of its own
+          while (peel < peel_max && peel + 32 < rest) {
+            const uint64_t l = h_len[m + h_ord[m + peel]];
+            if (l < (256u << 10) || l < 8 * median || l >= (1ull << 31)) break;
+            peel++;
+          }
+        }
+        items.push_back({m, rest - peel, 2});
+        for (size_t k = 0; k < peel; k++) items.push_back({m + h_ord[m + k], 1, 1});
+        ragged_skip = peel;
+      }
     }
     std::vector<cudaEvent_t> item_joins;
     for (size_t k = 0; k < items.size() && rc == TH_OK; k++) {
@@ -355,7 +375,7 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
       const uint8_t* pb = uni ? d_uni : (lone ? d_base + msgs[first].offset : d_base);
       const uint64_t* po = it.kind == 2 ? d_off : nullptr;
       const uint64_t* pl = it.kind == 2 ? d_len : nullptr;
-      const uint32_t* pr = it.kind == 2 ? d_ord : nullptr;
+      const uint32_t* pr = it.kind == 2 && d_ord ? d_ord + ragged_skip : nullptr;
       const uint64_t pstride = lone ? ((msgs[first].length + 15) & ~15ull) : ustride;
       const uint64_t plen = lone ? msgs[first].length : ulen;
       uint8_t* o = d_out + first * dlen[a];

@@ -604,3 +604,28 @@ def test_one_context_many_caller_threads(torch):
             x.join()
         assert not errors, errors[:4]
         assert e.stats()["submits"] == 48
+
+
+def test_heavy_tailed_batch_peels_outliers_into_lone_launches(eng):
+    """Many small messages plus a few far larger ones (>= 256 KiB, >= 8 x the median): the outliers leave the
+    per-lane launch for lone TMA launches (runtime.cu, launch items); digests and launch count say so."""
+    rng = np.random.default_rng(31)
+    lens = rng.integers(1, 20000, 500).tolist()
+    big = [300_000, 1_000_003, 262_144, 777_777, 2_500_000]
+    for k, b in enumerate(big):
+        lens.insert(37 + 91 * k, b)
+    bufs = [rng.integers(0, 256, int(n), dtype=np.uint8) for n in lens]
+    s0 = eng.stats()
+    out = eng.hash_batch(bufs, SHA1 | MD5 | SHA256)
+    s1 = eng.stats()
+    for a in (SHA1, MD5, SHA256):
+        wrong = np.nonzero((out[a] != ref_digests(a, bufs)).any(axis=1))[0]
+        assert wrong.size == 0, (NAMES[a], [lens[i] for i in wrong[:5]])
+    assert s1["launches"] - s0["launches"] == 3 * (1 + len(big))
+    # with a verify table the remainder stays one launch (the bitfield word is written by one ballot)
+    exp = ref_digests(SHA1, bufs).copy()
+    exp[40, 3] ^= 0x10
+    s0 = eng.stats()
+    out = eng.hash_batch(bufs, SHA1, expected_sha1=exp)
+    assert eng.stats()["launches"] - s0["launches"] == 1
+    assert np.nonzero(~out["ok"])[0].tolist() == [40]
