@@ -363,6 +363,134 @@ struct Tiles {
   static constexpr int WARP_BYTES = NST * STAGE_BYTES;  // tiles only; mbarriers live elsewhere
 };
 
+// ------------------------------------------------------------- ragged batches: cooperative row staging
+// Messages of unlike lengths at unrelated addresses cannot be described by one tensor map, and one bulk copy per
+// lane compiles to a 32-trip ELECT / R2UR / UBLKCP loop (38 % of the stall samples of that kernel).  Here the warp
+// fills the same swizzled {128 B x 32 rows} tiles with plain cp.async (SASS LDGSTS.128): thread t moves the
+// 16-byte piece (t & 7) of rows (t >> 3) + 4j, j = 0..7, so every instruction reads four whole 128-byte lines,
+// and the eight row pointers / lengths a thread serves are fetched once, by shuffle, for the whole stream.
+// The partial 16 bytes at a message's end are zero-filled by the copy's src-size; rows that have ended are skipped.
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// Hashes one message per lane (same contract as digest_stream).  smem: Tiles<K,NST>::WARP_BYTES, 1024-byte aligned.
+template <class A, int K, int NST>
+__device__ __forceinline__ void digest_stream_rows(const uint8_t* __restrict__ msg, uint64_t len, uint32_t* h,
+                                                   unsigned char* smem, int lane, uint32_t one) {
+  using T = Tiles<K, NST>;
+  constexpr int CH = T::CH;
+  constexpr unsigned FULL = 0xffffffffu;
+  const uint32_t s_base = smem_u32(smem);
+  const uint32_t piece = (uint32_t)lane & 7u, r0 = (uint32_t)lane >> 3;
+  const uint8_t* rp[8];
+  uint64_t rl[8];
+#pragma unroll
+  for (int j = 0; j < 8; j++) {
+    rp[j] = reinterpret_cast<const uint8_t*>(__shfl_sync(FULL, reinterpret_cast<unsigned long long>(msg), (int)r0 + 4 * j));
+    rl[j] = __shfl_sync(FULL, (unsigned long long)len, (int)r0 + 4 * j);
+  }
+  const uint32_t nch = (uint32_t)(len / CH) + 1u;  // as in digest_stream: the last chunk is partial (possibly empty)
+  const uint32_t last_bytes = (uint32_t)(len - (uint64_t)(nch - 1u) * CH);
+  const uint32_t max_nch = __reduce_max_sync(FULL, nch);
+  const uint32_t full_nch = __reduce_min_sync(FULL, nch) - 1u;  // chunks [0, full_nch) are whole in every row
+
+  auto issue = [&](uint32_t c, int s) {
+    const uint32_t d0 = s_base + (uint32_t)s * T::STAGE_BYTES;
+    if (c < full_nch) {  // warp-uniform fast path: no bounds to check
+      const uint64_t pos0 = (uint64_t)c * CH + piece * 16u;
+#pragma unroll
+      for (int j = 0; j < 8; j++) {
+        const uint32_t r = r0 + 4u * (uint32_t)j;
+        const uint32_t d = d0 + r * 128u + ((piece ^ (r & 7u)) << 4);
+        const uint8_t* src = rp[j] + pos0;
+#pragma unroll
+        for (int k = 0; k < K; k++) cp_async16(d + (uint32_t)k * T::TILE, src + k * 128, 16u);
+      }
+    } else if (c < max_nch) {
+      const uint64_t pos0 = (uint64_t)c * CH + piece * 16u;
+#pragma unroll
+      for (int j = 0; j < 8; j++) {
+        const uint32_t r = r0 + 4u * (uint32_t)j;
+        const uint32_t d = d0 + r * 128u + ((piece ^ (r & 7u)) << 4);
+        if (pos0 < rl[j]) {
+          const uint64_t rem64 = rl[j] - pos0;
+          const int rem = rem64 > (uint64_t)(CH + 16) ? CH + 16 : (int)rem64;
+          const uint8_t* src = rp[j] + pos0;
+#pragma unroll
+          for (int k = 0; k < K; k++) {
+            const int rk = rem - 128 * k;
+            if (rk > 0) cp_async16(d + (uint32_t)k * T::TILE, src + k * 128, rk >= 16 ? 16u : (uint32_t)rk);
+          }
+        }
+      }
+    }
+    cp_async_commit();  // one group per call, empty or not, so that wait_group counts stages
+  };
+
+#pragma unroll
+  for (int s = 0; s < NST; s++) issue((uint32_t)s, s);
+
+  A::init(h);
+  int s = 0;
+  const uint32_t my = s_base + (uint32_t)lane * 128u;
+  const uint32_t sw = (uint32_t)lane & 7u;
+  auto load_block = [&](uint32_t src, uint32_t bb, uint32_t* w) {
+    const uint32_t a = src + (bb >> 1) * T::TILE;
+    const uint32_t q0 = (bb & 1u) * 4u;
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+      uint4 v = lds128(a + (((q0 + (uint32_t)q) ^ sw) << 4));
+      w[4 * q] = v.x; w[4 * q + 1] = v.y; w[4 * q + 2] = v.z; w[4 * q + 3] = v.w;
+    }
+  };
+  for (uint32_t c = 0; c < max_nch; c++) {
+    cp_async_wait<NST - 1>();
+    __syncwarp();
+    const uint32_t src = my + (uint32_t)s * T::STAGE_BYTES;
+    // SHA-256 keeps ONE copy of its rounds: two would be 50 KB of code against a 32 KB instruction cache, and
+    // warps in the tail loop beside warps in the body loop thrash it (measured 930 -> 800 GB/s).
+    if (A::DLEN != 32 && c < full_nch) {  // every lane has CH / 64 whole blocks here: no padding logic in this loop
+#pragma unroll 1
+      for (uint32_t b = 0; b < (uint32_t)(CH / 64); b++) {
+        uint32_t w[16];
+        load_block(src, b, w);
+        if (A::BE) {
+#pragma unroll
+          for (int i = 0; i < 16; i++) w[i] = bswap(w[i]);
+        }
+        A::compress(h, w, one);
+      }
+    } else if (c < nch) {
+      const bool last = c == nch - 1u;
+      const uint32_t bytes = last ? last_bytes : (uint32_t)CH;
+      const uint32_t nb = bytes >> 6;
+      const uint32_t r = bytes & 63u;
+      const uint32_t nblk = nb + (last ? (r < 56 ? 1u : 2u) : 0u);
+#pragma unroll 1
+      for (uint32_t b = 0; b < nblk; b++) {
+        uint32_t w[16];
+        load_block(src, b < (uint32_t)(CH / 64) ? b : 0u, w);  // a second padding block reads nothing it keeps
+        if (b >= nb) pad_block<A>(w, b - nb, r, len);
+        if (A::BE) {
+#pragma unroll
+          for (int i = 0; i < 16; i++) w[i] = bswap(w[i]);
+        }
+        A::compress(h, w, one);
+      }
+    }
+    __syncwarp();  // all lanes are done reading this stage before any lane's copies overwrite it
+    issue(c + NST, s);
+    if (++s == NST) s = 0;
+  }
+  cp_async_wait<0>();
+}
+
 // Per-warp pipeline state that survives across segments (stage cursor + one phase bit per stage).
 struct PipeState {
   int stage = 0;

@@ -1,6 +1,7 @@
 // kernels.cu — sm_100a kernels and the launch-level C ABI (include/tritonhash.h, last section).
 //
-//   digest_kernel<A,CH,NST>  one warp = one CTA = 32 messages; th::digest_stream does the work.
+//   digest_rows_kernel<A,K,NST> / digest_kernel<A,CH,NST>  one warp = one CTA = 32 messages of any lengths;
+//                            th::digest_stream_rows (default) / th::digest_stream do the work.
 //                            SHA-1 adds the fused compare -> verified bitfield ([dep] webtorrent
 //                            `hash === _hashes[index]` -> bitfield.set(index); lib/download.js:64-66).
 //   etag_kernel              one warp per multipart object, md5 over its part digests, message words
@@ -32,24 +33,26 @@ struct DigestArgs {
   uint32_t one;             // the value 1, opaque to the compiler (see add_fma)
 };
 
-template <class A, int CH, int NST>
-__global__ void __launch_bounds__(32) digest_kernel(const DigestArgs p) {
-  extern __shared__ __align__(1024) unsigned char smem[];
-  const int lane = threadIdx.x;
-  const uint32_t slot = blockIdx.x * 32u + lane;
+// Which message a lane hashes: slot -> (order) -> offset / length.
+__device__ __forceinline__ bool lane_message(const DigestArgs& p, int lane, uint32_t* idx, uint64_t* off, uint64_t* len) {
+  const uint32_t slot = blockIdx.x * 32u + (uint32_t)lane;
   const bool valid = slot < p.n;
-  uint32_t idx = slot;
-  if (valid && p.order) idx = p.order[slot];
-  uint64_t off = 0, len = 0;
+  *idx = slot;
+  if (valid && p.order) *idx = p.order[slot];
+  *off = 0;
+  *len = 0;
   if (valid) {
-    off = p.offsets ? p.offsets[idx] : (uint64_t)idx * p.stride;
-    len = p.lengths ? p.lengths[idx] : p.len;
+    *off = p.offsets ? p.offsets[*idx] : (uint64_t)*idx * p.stride;
+    *len = p.lengths ? p.lengths[*idx] : p.len;
   }
-  uint32_t h[A::NS];
-  digest_stream<A, CH, NST>(p.base + off, len, h, smem, lane, p.one);
-  if (valid) store_digest<A>(p.out + (size_t)idx * A::DLEN, h);
+  return valid;
+}
 
-  if (A::DLEN == 20 && p.expected && p.ok_bits) {  // fused piece verification
+// Digest store + (SHA-1) fused piece verification for the per-lane kernels.
+template <class A>
+__device__ __forceinline__ void lane_finish(const DigestArgs& p, int lane, bool valid, uint32_t idx, const uint32_t* h) {
+  if (valid) store_digest<A>(p.out + (size_t)idx * A::DLEN, h);
+  if (A::DLEN == 20 && p.expected && p.ok_bits) {
     bool ok = false;
     if (valid) {
       const uint32_t* e = reinterpret_cast<const uint32_t*>(p.expected + (size_t)idx * 20);
@@ -64,6 +67,31 @@ __global__ void __launch_bounds__(32) digest_kernel(const DigestArgs p) {
       if (lane == 0) p.ok_bits[blockIdx.x] = word;
     }
   }
+}
+
+template <class A, int CH, int NST>
+__global__ void __launch_bounds__(32) digest_kernel(const DigestArgs p) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  const int lane = threadIdx.x;
+  uint32_t idx;
+  uint64_t off, len;
+  const bool valid = lane_message(p, lane, &idx, &off, &len);
+  uint32_t h[A::NS];
+  digest_stream<A, CH, NST>(p.base + off, len, h, smem, lane, p.one);
+  lane_finish<A>(p, lane, valid, idx, h);
+}
+
+// Same contract, staged by cooperative cp.async into swizzled row tiles (digest_stream_rows): the ragged default.
+template <class A, int K, int NST>
+__global__ void __launch_bounds__(32) digest_rows_kernel(const DigestArgs p) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  const int lane = threadIdx.x;
+  uint32_t idx;
+  uint64_t off, len;
+  const bool valid = lane_message(p, lane, &idx, &off, &len);
+  uint32_t h[A::NS];
+  digest_stream_rows<A, K, NST>(p.base + off, len, h, smem, lane, p.one);
+  lane_finish<A>(p, lane, valid, idx, h);
 }
 
 // --------------------------------------------------------------- equal-length batches: tensor-map path
@@ -362,6 +390,21 @@ cudaError_t launch_variant(const DigestArgs& a, cudaStream_t st) {
   return cudaGetLastError();
 }
 
+template <class A, int K, int NST>
+cudaError_t launch_rows(const DigestArgs& a, cudaStream_t st) {
+  constexpr int smem = Tiles<K, NST>::WARP_BYTES;
+  static bool done[64] = {};
+  cudaError_t e0 = allow_smem(digest_rows_kernel<A, K, NST>, done, smem);
+  if (e0 != cudaSuccess) return e0;
+  digest_rows_kernel<A, K, NST><<<(a.n + 31u) / 32u, 32, smem, st>>>(a);
+  return cudaGetLastError();
+}
+
+struct RowsVariant { int k, nst; launch_fn fn[3]; };
+#define TH_ROWS(K, N) {K, N, {launch_rows<Sha1, K, N>, launch_rows<Md5, K, N>, launch_rows<Sha256, K, N>}}
+static const RowsVariant g_rows_variants[] = {TH_ROWS(1, 3), TH_ROWS(1, 4), TH_ROWS(2, 2), TH_ROWS(2, 3), TH_ROWS(4, 2)};
+constexpr int kNumRowsVariants = (int)(sizeof(g_rows_variants) / sizeof(g_rows_variants[0]));
+
 // ---- tensor-map path (equal-length, fixed-stride batches) -------------------------------------------
 using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -402,6 +445,8 @@ struct TileOpts {
   int sliced_min_groups = 592;  // auto: use the sliced kernel from this many 32-message groups
   int tile_many_groups = 8192;  // auto: SHA-1 / SHA-256 batches with at least this many groups go back to one-warp CTAs
                                 // (many waves balance themselves and measured 1-12 % faster than the persistent kernel)
+  int ragged_rows = 1;          // per-lane kernels: 1 = cooperative cp.async row tiles, 0 = one bulk copy per lane
+  int rows_variant[3] = {2, 2, 2};  // index into g_rows_variants per digest
 };
 static TileOpts g_opts;
 
@@ -583,7 +628,8 @@ static int launch_digest(uint32_t alg, const void* d_base, const uint64_t* d_off
   }
   DigestArgs a{static_cast<const uint8_t*>(d_base), d_offsets, d_lengths, d_order, stride, len, n, d_out,
                d_expected, d_ok_bits, 1u};
-  cudaError_t e = g_variants[g_selected[ai]].fn[ai](a, static_cast<cudaStream_t>(stream));
+  cudaError_t e = g_opts.ragged_rows ? g_rows_variants[g_opts.rows_variant[ai]].fn[ai](a, static_cast<cudaStream_t>(stream))
+                                    : g_variants[g_selected[ai]].fn[ai](a, static_cast<cudaStream_t>(stream));
   return e == cudaSuccess ? TH_OK : TH_ECUDA;
 }
 
@@ -737,6 +783,12 @@ int th_set_option(const char* name, long long value) {
   if (k == "rounds") { if (value < 1 || value > 4096) return TH_EINVAL; th::g_opts.rounds = (int)value; return TH_OK; }
   if (k == "tile_many_groups") { if (value < 1) return TH_EINVAL; th::g_opts.tile_many_groups = (int)value; return TH_OK; }
   if (k == "sliced_min_groups") { if (value < 1) return TH_EINVAL; th::g_opts.sliced_min_groups = (int)value; return TH_OK; }
+  if (k == "ragged_rows") { if (value < 0 || value > 1) return TH_EINVAL; th::g_opts.ragged_rows = (int)value; return TH_OK; }
+  if (k == "rows_variant") {
+    if (value < 0 || value >= th::kNumRowsVariants) return TH_EINVAL;
+    for (int a = 0; a < 3; a++) th::g_opts.rows_variant[a] = (int)value;
+    return TH_OK;
+  }
   if (k == "tile_k" || k == "tile_stages") return TH_EINVAL;  // use th_set_tiling
   return TH_EINVAL;
 }
@@ -758,7 +810,11 @@ int th_plan(uint32_t alg, uint64_t len, uint64_t stride, uint32_t n, char* out, 
   const th::Plan pl = th::make_plan(ai, stride, len, n);
   if (pl.path == 1) {
     const th::Variant& v = th::g_variants[th::g_selected[ai]];
-    snprintf(out, cap, "bulk: one-warp CTAs, per-lane cp.async.bulk, %d B x %d stages, grid %u", v.ch, v.nst, (n + 31u) / 32u);
+    const th::RowsVariant& r = th::g_rows_variants[th::g_opts.rows_variant[ai]];
+    if (th::g_opts.ragged_rows)
+      snprintf(out, cap, "rows: one-warp CTAs, cooperative cp.async into {128B x 32 msgs} x %d tiles x %d stages, grid %u", r.k, r.nst, (n + 31u) / 32u);
+    else
+      snprintf(out, cap, "bulk: one-warp CTAs, per-lane cp.async.bulk, %d B x %d stages, grid %u", v.ch, v.nst, (n + 31u) / 32u);
   } else if (pl.path == 4) {
     snprintf(out, cap,
              "assist: %u CTAs x (chain warp + schedule-helper warp), TMA 2-D {128B x 32 msgs} x %d tiles x %d stages, "

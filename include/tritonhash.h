@@ -198,10 +198,12 @@ int th_get_staging(uint32_t alg, int* chunk_bytes, int* stages);
  * but the last) take the tensor-map kernels: a {128 B x 32 messages} TMA box per copy.  This picks how
  * many such tiles a warp stages per pipeline stage (1, 2, 4) and the number of stages (2..4). */
 int th_set_tiling(uint32_t alg, int tiles_per_stage, int stages);
-/* Tuning knobs (process-wide): "path" 0 auto | 1 per-lane bulk copies | 2 one-warp CTAs on tensor-map
+/* Tuning knobs (process-wide): "path" 0 auto | 1 the ragged engine for every batch | 2 one-warp CTAs on tensor-map
  * tiles | 3 persistent time-sliced kernel | 4 chain + schedule-helper warp per group (SHA-1/SHA-256, few
  * large messages); "workers" 4|8|12|16 warps per SM for path 3; "rounds" scheduling rounds per worker for
- * path 3; "sliced_min_groups" / "assist_max_groups" / "tile_many_groups" auto thresholds (in 32-message groups). */
+ * path 3; "sliced_min_groups" / "assist_max_groups" / "tile_many_groups" auto thresholds (in 32-message groups);
+ * "ragged_rows" 1 (default) cooperative cp.async row tiles | 0 one bulk copy per lane (th_set_staging geometry)
+ * for batches of unlike lengths; "rows_variant" 0..4 = (tiles, stages) (1,3) (1,4) (2,2) (2,3) (4,2) of the former. */
 int th_set_option(const char* name, long long value);
 /* Describes, as text, the kernel and geometry an equal-length batch of n messages would be run
  * with on the current device (what benchmarks record next to their numbers). */

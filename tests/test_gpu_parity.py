@@ -79,6 +79,7 @@ def test_all_staging_variants(eng, L, ch, nst):
     ch0, st0 = C.c_int(), C.c_int()
     L.th_get_staging(1, C.byref(ch0), C.byref(st0))
     try:
+        assert L.th_set_option(b"ragged_rows", 0) == 0  # the per-lane bulk-copy engine (no longer the default)
         assert L.th_set_staging(7, ch, nst) == 0
         lens = [0, 1, 15, 16, 17, 55, 56, 63, 64, 65, ch - 1, ch, ch + 1, ch + 55, ch + 56, 2 * ch, 3 * ch + 63,
                 nst * ch, nst * ch + 1, (nst + 1) * ch - 8, 5000, 70001] + list(range(1000, 1040))
@@ -88,6 +89,25 @@ def test_all_staging_variants(eng, L, ch, nst):
             assert (out[alg] == ref_digests(alg, bufs)).all(), (NAMES[alg], ch, nst)
     finally:
         assert L.th_set_staging(7, ch0.value, st0.value) == 0
+        assert L.th_set_option(b"ragged_rows", 1) == 0
+
+
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4])
+def test_all_row_staging_variants(eng, L, variant):
+    """The ragged default: cooperative cp.async into swizzled row tiles, every compiled (tiles, stages) geometry."""
+    k, nst = [(1, 3), (1, 4), (2, 2), (2, 3), (4, 2)][variant]
+    ch = 128 * k
+    try:
+        assert L.th_set_option(b"rows_variant", variant) == 0
+        lens = [0, 1, 15, 16, 17, 55, 56, 63, 64, 65, 119, 120, 127, 128, 129, ch - 1, ch, ch + 1, ch + 55, ch + 56,
+                2 * ch, 3 * ch + 63, nst * ch, nst * ch + 1, (nst + 1) * ch - 8, 5000, 70001, 300001] + list(range(1000, 1040))
+        bufs = [oracle.synth(i, n) for i, n in enumerate(lens)]
+        out = eng.hash_batch(bufs, ALL)
+        for alg in (SHA1, MD5, SHA256):
+            wrong = np.nonzero((out[alg] != ref_digests(alg, bufs)).any(axis=1))[0]
+            assert wrong.size == 0, (NAMES[alg], k, nst, [lens[i] for i in wrong[:6]])
+    finally:
+        assert L.th_set_option(b"rows_variant", 2) == 0
 
 
 def test_synth_fill_matches_oracle_generator(torch, L):

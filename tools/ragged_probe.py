@@ -19,6 +19,9 @@ NAME = {ALG_SHA1: "sha1", ALG_MD5: "md5", ALG_SHA256: "sha256"}
 
 
 def main():
+    for kv in sys.argv[1:]:  # th_set_option pairs, e.g. ragged_rows=0 rows_variant=3
+        k, v = kv.split("=")
+        assert _capi.lib().th_set_option(k.encode(), int(v)) == 0, kv
     rng = np.random.default_rng(5)
     dists = {
         "uniform 1..64 KiB x 200k": rng.integers(1, 65536, 200_000),
