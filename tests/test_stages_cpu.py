@@ -126,6 +126,30 @@ def test_concat_files_reads_across_boundaries(tmp_path):
     assert piece_bounds(10, 4) == [(0, 4), (4, 8), (8, 10)]
 
 
+def test_concat_files_chunked_thread_pool_reads(tmp_path, monkeypatch):
+    """Large ranges are cut into chunks read by a thread pool; same bytes as the serial read, short file included."""
+    from downloader_b200 import reader
+    monkeypatch.setattr(reader, "READ_CHUNK", 1000)
+    monkeypatch.setattr(reader, "READ_THREADS", 4)
+    sizes = [12345, 7, 50000]
+    blob = oracle.synth(2, sum(sizes)).tobytes()
+    files, pos = [], 0
+    for i, n in enumerate(sizes):
+        p = tmp_path / f"g{i}"
+        p.write_bytes(blob[pos:pos + n] if i != 2 else blob[pos:pos + n - 3000])  # last file is 3000 bytes short on disk
+        files.append((str(p), n))
+        pos += n
+    exp_all = blob[:sum(sizes) - 3000] + bytes(3000)
+    src = _ConcatFiles(files)
+    try:
+        for start, ln in [(0, sum(sizes)), (999, 30001), (12340, 20), (60000, 2352 + 100)]:
+            buf = np.full(ln, 0xEE, np.uint8)
+            src.readinto(buf, start)
+            assert buf.tobytes() == exp_all[start:start + ln].ljust(ln, b"\0"), (start, ln)
+    finally:
+        src.close()
+
+
 def test_s3_mock_plays_the_server():
     m = S3Mock()
     assert not m.bucketExists("b")
