@@ -377,8 +377,7 @@ def main():
                "d2h_bytes_per_step": int((s1["d2h_bytes"] - s0["d2h_bytes"]) // e2e_steps),
                "messages_per_gpu": slots * per_slot, "steps": e2e_steps, "ms_per_step": round(dt * 1e3, 3), "timing": "host wall clock around %d streamed steps (submit all slots, collect the previous step's digests; last step drained inside), max over ranks" % e2e_steps,
                "pinned_ring_bytes": slots * slot_bytes, "device_ring_bytes": dev_mult * slots * slot_bytes,
-               "launches_per_step": int((s1["launches"] - s0["launches"]) // e2e_steps),
-               "kernel_ms_per_step": round((s1["kernel_ms"] - s0["kernel_ms"]) / e2e_steps, 3)}
+               "launches_per_step": int((s1["launches"] - s0["launches"]) // e2e_steps)}
         eng.close()
     sampler.stop()
     clocks = sampler.summary(t0, t1)

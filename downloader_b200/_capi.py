@@ -98,6 +98,7 @@ def lib() -> C.CDLL:
     L.th_get_staging.argtypes = [u32, C.POINTER(i32), C.POINTER(i32)]
     L.th_set_tiling.argtypes = [u32, i32, i32]
     L.th_set_option.argtypes = [C.c_char_p, C.c_longlong]
+    L.th_set_ticket_timing.argtypes = [vp, C.c_int]
     L.th_plan.argtypes = [u32, u64, u64, u32, C.c_char_p, C.c_size_t]
     _lib = L
     return L

@@ -10,6 +10,7 @@
 //
 // There is no CPU fallback: every path ends in a kernel of kernels.cu or fails with an error code.
 #include <algorithm>
+#include <atomic>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -71,15 +72,20 @@ struct Ticket {
   size_t n = 0;
   uint32_t mask = 0;
   bool has_expected = false;
-  bool finished = false;       // ev_done observed
+  bool finished = false;       // every tail's `done` event observed
   bool timed = false;
   int status = TH_OK;
   JobBuf* jb = nullptr;
   uint64_t slot_id = 0;        // 0 = device-resident submit
-  cudaEvent_t ev_done = nullptr;
+  // One entry per launch item: the end of its kernel (timing) and of its digest copy-back.  A ticket is joined
+  // on the HOST over these events — never by one stream waiting for another: a stream parked on an event of a
+  // 0.25..1 s chain also parks every stream that shares its hardware queue (120 streams share 32 queues).
+  struct Tail { cudaEvent_t k_end; cudaEvent_t done; int alg; };
+  std::vector<Tail> tails;
+  std::atomic<int> cb_left{0};  // launch items that have not reached their host callback yet
   cudaEvent_t ev_ready = nullptr;  // inputs (payload + descriptors) on the device; timing-enabled
   double times_ms[7] = {-1, -1, -1, -1, -1, -1, -1};  // since th_init: ready, then start / end per digest
-  cudaEvent_t ev_k0[3] = {nullptr, nullptr, nullptr}, ev_k1[3] = {nullptr, nullptr, nullptr};
+  cudaEvent_t ev_k0[3] = {nullptr, nullptr, nullptr};  // start of each digest's first launch item
   th_done_cb cb = nullptr;
   void* user = nullptr;
   struct th_ctx* ctx = nullptr;
@@ -88,11 +94,11 @@ struct Ticket {
 // Kernels of different submits must be able to overlap: a slot of large parts holds only a few message
 // groups, and a chain's latency (0.26 s for a 16 MiB SHA-256 part) is far longer than the slot's H2D copy.
 // Tickets therefore rotate over a pool of stream sets; only the H2D copies share one stream (one PCIe link).
-constexpr int kStreamSets = 10;      // default
-constexpr int kMaxStreamSets = 40;   // TRITONHASH_STREAM_SETS may ask for more (streams then alias on the 32 queues)
-// 10 sets x 3 digest streams + copy + misc = 32 streams: exactly the 32 hardware work queues a process can ask
-// for (CUDA_DEVICE_MAX_CONNECTIONS, set in th_init when CUDA is not initialised yet).  With the default of 8
-// queues streams alias, and a D2H copy queued behind a 0.26 s kernel stalls unrelated kernels in its queue.
+constexpr int kStreamSets = 40;      // default: 120 digest streams (the GPU runs up to 128 kernels at once)
+constexpr int kMaxStreamSets = 40;   // TRITONHASH_STREAM_SETS narrows the rotation
+constexpr int kTimedStreamSets = 10; // with ticket timing on: 30 streams + copy + misc = the 32 hardware queues
+// Streams beyond the 32 hardware work queues (CUDA_DEVICE_MAX_CONNECTIONS, set in th_init when CUDA is not
+// initialised yet) share queues; that is harmless as long as nothing queued behind a long kernel waits for it.
 struct StreamSet {
   cudaStream_t alg[3] = {nullptr, nullptr, nullptr};
 };
@@ -134,6 +140,11 @@ struct th_ctx {
   uint64_t next_id = 1;
   std::string last_error;
   int sticky = TH_OK;
+  // Per-ticket device timeline (th_ticket_timing, th_stats.kernel_ms).  OFF by default: a timing-enabled event
+  // recorded behind a kernel holds its hardware queue until the kernel ends (measured, tools/microbench/queues.cu:
+  // 128 streams of 50 ms kernels take 50 ms with plain events and 200 ms with timing events), which caps the
+  // long chains of large parts at 32 at a time.  When on, the rotation keeps to 10 stream sets (one queue each).
+  bool timing = false;
 };
 
 namespace {
@@ -244,6 +255,8 @@ size_t ring_fit(size_t cap, size_t head, size_t tail, bool idle, size_t need) {
   return (size_t)-1;
 }
 
+cudaError_t ticket_poll(Ticket* t, bool block);
+
 // Marks copied slots' pinned bytes and finished slots' device bytes reusable and advances both ring heads.
 void reap(th_ctx* c, Gpu& g, bool block_on_oldest) {
   for (auto& s : g.slots) {
@@ -254,8 +267,7 @@ void reap(th_ctx* c, Gpu& g, bool block_on_oldest) {
       if (it == c->tickets.end()) continue;  // already retired by th_result
       Ticket* t = it->second;
       if (!t->finished) {
-        cudaError_t e = (block_on_oldest && &s == &g.slots.front()) ? cudaEventSynchronize(t->ev_done)
-                                                                    : cudaEventQuery(t->ev_done);
+        cudaError_t e = ticket_poll(t, block_on_oldest && &s == &g.slots.front());
         if (e == cudaSuccess) t->finished = true;
         else if (e != cudaErrorNotReady) { t->finished = true; t->status = cuda_fail(c, e, "ticket event"); }
       }
@@ -275,9 +287,19 @@ void reap(th_ctx* c, Gpu& g, bool block_on_oldest) {
   else g.head = g.tail = 0;
 }
 
-void CUDART_CB host_done(void* p) {
+// Runs on CUDA's callback thread once per launch item; the item that finishes last delivers the ticket's callback.
+void CUDART_CB host_item_done(void* p) {
   Ticket* t = static_cast<Ticket*>(p);
-  if (t->cb) t->cb(t->user, t->id, TH_OK);
+  if (t->cb_left.fetch_sub(1) == 1 && t->cb) t->cb(t->user, t->id, TH_OK);
+}
+
+// cudaEventQuery / cudaEventSynchronize over every tail of a ticket.
+cudaError_t ticket_poll(Ticket* t, bool block) {
+  for (auto& tl : t->tails) {
+    cudaError_t e = block ? cudaEventSynchronize(tl.done) : cudaEventQuery(tl.done);
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
 }
 
 int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, const th_msg* msgs, size_t n,
@@ -325,7 +347,7 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
   CU(c, cudaMemcpyAsync(jb->d, jb->h, desc_bytes, cudaMemcpyHostToDevice, g.s_copy));
   g.st.h2d_bytes += desc_bytes;
   cudaEvent_t ev_in;
-  CU(c, cudaEventCreate(&ev_in));
+  CU(c, cudaEventCreateWithFlags(&ev_in, c->timing ? cudaEventDefault : cudaEventDisableTiming));
   CU(c, cudaEventRecord(ev_in, g.s_copy));
   t->ev_ready = ev_in;
 
@@ -333,38 +355,23 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
   const uint64_t* d_len = reinterpret_cast<const uint64_t*>(jb->d + jb->o_len(n)) + m;
   const uint32_t* d_ord = use_order ? reinterpret_cast<const uint32_t*>(jb->d + jb->o_ord(n)) + m : nullptr;
   const size_t out_off[3] = {jb->o_sha1(n), jb->o_md5(n), jb->o_sha256(n)};
-  const size_t out_len[3] = {n * 20, n * 16, n * 32};
   const size_t dlen[3] = {20, 16, 32};
   const size_t ok_bytes = ((n + 31) / 32) * 4;
   const uint8_t* d_uni = d_base + msgs[0].offset;
-  cudaStream_t tstream[3] = {nullptr, nullptr, nullptr};
-  int primary = -1;
-  std::vector<cudaEvent_t> joins;
 
-  for (int a = 0; a < 3; a++) {
-    if (!(mask & (1u << a))) continue;
-    cudaStream_t st = g.sets[g.next_stream[a]++ % (uint64_t)g.n_sets].alg[a];
-    tstream[a] = st;
-    CU(c, cudaStreamWaitEvent(st, ev_in, 0));
-    int rc = TH_OK;
-    CU(c, cudaEventCreate(&t->ev_k0[a]));
-    CU(c, cudaEventCreate(&t->ev_k1[a]));
-    uint8_t* d_out = jb->d + out_off[a];
-    const uint8_t* d_exp = (a == 0 && expected) ? jb->d + jb->o_exp(n) : nullptr;
-    uint32_t* d_ok = (a == 0 && expected) ? reinterpret_cast<uint32_t*>(jb->d + jb->o_ok(n)) : nullptr;
-    if (d_ok && use_order) CU(c, cudaMemsetAsync(d_ok + m / 32, 0, ok_bytes - (m / 32) * 4, st));
-    CU(c, cudaEventRecord(t->ev_k0[a], st));
-    // Launch items: the equal-length prefix (tensor-map kernels), then the remainder.  A remainder of a few LARGE
-    // messages (the short last piece / part, or a handful of whole-file bodies) is launched message by message as
-    // "equal-length batches of one": each gets the TMA path and, for SHA-1 / SHA-256, the schedule-helper warp,
-    // which halves its chain latency compared with the per-lane kernel.  Everything after the first item runs on
-    // further streams of this digest's rotation and is joined before the digests are copied back.
-    struct Item { size_t first, cnt; int kind; };  // kind 0 prefix, 1 lone, 2 ragged
+  // Launch items: the equal-length prefix (tensor-map kernels), then the remainder.  A remainder of a few LARGE
+  // messages (the short last piece / part, or a handful of whole-file bodies) is launched message by message as
+  // "equal-length batches of one": each gets the TMA path and, for SHA-1 / SHA-256, the schedule-helper warp,
+  // which halves its chain latency compared with the per-lane kernel.  Every item after a digest's first runs on
+  // another stream of the rotation; each item copies back the digests it produced on its own stream.
+  struct Item { size_t first, cnt; int kind; };  // kind 0 prefix, 1 lone, 2 per-lane remainder
+  auto build_items = [&](int a, size_t* skip) {
     std::vector<Item> items;
-    size_t ragged_skip = 0;  // leading entries of the order that are launched alone
+    const bool verify = a == 0 && expected;
+    *skip = 0;
     if (m) items.push_back({0, m, 0});
     if (rest) {
-      bool lone_ok = rest <= 64 && !(d_ok && rest > 1);
+      bool lone_ok = rest <= 64 && !(verify && rest > 1);
       for (size_t i = m; i < n && lone_ok; i++)
         lone_ok = msgs[i].length < (1ull << 31) && msgs[i].length >= (rest == 1 ? 1024u : (256u << 10));
       if (lone_ok) {
@@ -375,9 +382,9 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
         // few outliers (>= 256 KiB and >= 8 x the median; they lead the descending order; at most 8) are peeled into lone
         // launches; the per-lane launch takes the rest of the order.
         size_t peel = 0;
-        if (use_order && !d_ok) {
+        if (use_order && !verify) {
           const uint64_t median = h_len[m + h_ord[m + rest / 2]];
-          const size_t peel_max = (size_t)std::max(1, g.n_sets - 2);  // each lone launch wants a stream of its own
+          const size_t peel_max = 8;
           while (peel < peel_max && peel + 32 < rest) {
             const uint64_t l = h_len[m + h_ord[m + peel]];
             if (l < (256u << 10) || l < 8 * median || l >= (1ull << 31)) break;
@@ -386,15 +393,38 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
         }
         items.push_back({m, rest - peel, 2});
         for (size_t k = 0; k < peel; k++) items.push_back({m + h_ord[m + k], 1, 1});
-        ragged_skip = peel;
+        *skip = peel;
       }
     }
-    std::vector<cudaEvent_t> item_joins;
+    return items;
+  };
+  const uint64_t sets = (uint64_t)(c->timing ? std::min(g.n_sets, kTimedStreamSets) : g.n_sets);
+  int n_items = 0;
+  for (int a = 0; a < 3; a++) {
+    size_t skip;
+    if (mask & (1u << a)) n_items += (int)build_items(a, &skip).size();
+  }
+  t->cb_left.store(n_items);
+  t->tails.reserve((size_t)n_items);
+
+  for (int a = 0; a < 3; a++) {
+    if (!(mask & (1u << a))) continue;
+    cudaStream_t st = g.sets[g.next_stream[a]++ % sets].alg[a];
+    CU(c, cudaStreamWaitEvent(st, ev_in, 0));
+    int rc = TH_OK;
+    if (c->timing) CU(c, cudaEventCreate(&t->ev_k0[a]));
+    uint8_t* d_out = jb->d + out_off[a];
+    const uint8_t* d_exp = (a == 0 && expected) ? jb->d + jb->o_exp(n) : nullptr;
+    uint32_t* d_ok = (a == 0 && expected) ? reinterpret_cast<uint32_t*>(jb->d + jb->o_ok(n)) : nullptr;
+    if (d_ok && use_order) CU(c, cudaMemsetAsync(d_ok + m / 32, 0, ok_bytes - (m / 32) * 4, st));
+    if (c->timing) CU(c, cudaEventRecord(t->ev_k0[a], st));
+    size_t ragged_skip = 0;  // leading entries of the order that are launched alone
+    const std::vector<Item> items = build_items(a, &ragged_skip);
     for (size_t k = 0; k < items.size() && rc == TH_OK; k++) {
       const Item& it = items[k];
       cudaStream_t ps = st;
       if (k > 0 && !(it.kind == 2 && d_ok && use_order)) {  // (the bitfield memset above is ordered on st only)
-        ps = g.sets[g.next_stream[a]++ % (uint64_t)g.n_sets].alg[a];
+        ps = g.sets[g.next_stream[a]++ % sets].alg[a];
         CU(c, cudaStreamWaitEvent(ps, ev_in, 0));
       }
       const bool uni = it.kind == 0, lone = it.kind == 1;
@@ -413,49 +443,49 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
         rc = th_md5_batch(pb, po, pl, pr, pstride, plen, (uint32_t)it.cnt, o, ps);
       else
         rc = th_sha256_batch(pb, po, pl, pr, pstride, plen, (uint32_t)it.cnt, o, ps);
+      if (rc != TH_OK) break;
       g.st.launches += 1;
-      if (ps != st && rc == TH_OK) {
-        cudaEvent_t ev;
-        CU(c, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-        CU(c, cudaEventRecord(ev, ps));
-        item_joins.push_back(ev);
+      Ticket::Tail tl{nullptr, nullptr, a};
+      if (c->timing) {
+        CU(c, cudaEventCreate(&tl.k_end));
+        CU(c, cudaEventRecord(tl.k_end, ps));
       }
-    }
-    for (cudaEvent_t ev : item_joins) {
-      CU(c, cudaStreamWaitEvent(st, ev, 0));
-      CU(c, cudaEventDestroy(ev));
+      // Copy back what this item wrote.  The per-lane remainder writes at original indices all over [m, n) except
+      // the peeled messages', which their own items copy: its range is cut around those (two copies of one host
+      // byte from different streams must not be in flight together).
+      const size_t span = it.kind == 2 ? rest : it.cnt;
+      std::vector<size_t> holes;
+      if (it.kind == 2)
+        for (size_t q = 0; q < ragged_skip; q++) holes.push_back(m + h_ord[m + q]);
+      std::sort(holes.begin(), holes.end());
+      holes.push_back(first + span);
+      size_t lo = first;
+      for (size_t hole : holes) {
+        if (hole > lo) {
+          CU(c, cudaMemcpyAsync(jb->h + out_off[a] + lo * dlen[a], jb->d + out_off[a] + lo * dlen[a], (hole - lo) * dlen[a],
+                                cudaMemcpyDeviceToHost, ps));
+          g.st.d2h_bytes += (hole - lo) * dlen[a];
+        }
+        lo = hole + 1;
+      }
+      if (d_ok) {  // the bitfield words this item produced (items split on word boundaries)
+        const size_t w0 = first / 32, w1 = (first + span + 31) / 32;
+        CU(c, cudaMemcpyAsync(jb->h + jb->o_ok(n) + w0 * 4, jb->d + jb->o_ok(n) + w0 * 4, (w1 - w0) * 4, cudaMemcpyDeviceToHost, ps));
+        g.st.d2h_bytes += (w1 - w0) * 4;
+      }
+      // the callback is enqueued before `done` so that a ticket cannot be retired (th_result waits on every
+      // `done`) while one of its callbacks is still pending
+      if (t->cb) CU(c, cudaLaunchHostFunc(ps, host_item_done, t));
+      CU(c, cudaEventCreateWithFlags(&tl.done, cudaEventDisableTiming));
+      CU(c, cudaEventRecord(tl.done, ps));
+      t->tails.push_back(tl);
     }
     if (rc != TH_OK) {
       if (rc == TH_ECUDA) return cuda_fail(c, cudaGetLastError(), "digest kernel launch");
       return rc;
     }
-    CU(c, cudaEventRecord(t->ev_k1[a], st));
     g.st.messages += n;
-    CU(c, cudaMemcpyAsync(jb->h + out_off[a], jb->d + out_off[a], out_len[a], cudaMemcpyDeviceToHost, st));
-    g.st.d2h_bytes += out_len[a];
-    if (a == 0 && expected) {
-      CU(c, cudaMemcpyAsync(jb->h + jb->o_ok(n), jb->d + jb->o_ok(n), ok_bytes, cudaMemcpyDeviceToHost, st));
-      g.st.d2h_bytes += ok_bytes;
-    }
-    if (primary < 0) {
-      primary = a;  // the first requested digest's stream also carries the ticket's completion
-    } else {
-      cudaEvent_t ev_a;
-      CU(c, cudaEventCreateWithFlags(&ev_a, cudaEventDisableTiming));
-      CU(c, cudaEventRecord(ev_a, st));
-      joins.push_back(ev_a);
-    }
   }
-  cudaStream_t sp = tstream[primary];
-  for (cudaEvent_t ev : joins) {
-    CU(c, cudaStreamWaitEvent(sp, ev, 0));
-    CU(c, cudaEventDestroy(ev));
-  }
-  // the callback is enqueued before ev_done so that a ticket cannot be retired (th_result waits on
-  // ev_done) while its callback is still pending
-  if (t->cb) CU(c, cudaLaunchHostFunc(sp, host_done, t));
-  CU(c, cudaEventCreateWithFlags(&t->ev_done, cudaEventDisableTiming));
-  CU(c, cudaEventRecord(t->ev_done, sp));
   g.st.bytes += total;
   g.st.submits += 1;
   return TH_OK;
@@ -474,11 +504,14 @@ int validate(const th_msg* msgs, size_t n, uint32_t mask, size_t limit) {
 }
 
 void free_ticket_events(Ticket* t) {
-  if (t->ev_done) cudaEventDestroy(t->ev_done);
+  for (auto& tl : t->tails) {
+    if (tl.k_end) cudaEventDestroy(tl.k_end);
+    if (tl.done) cudaEventDestroy(tl.done);
+  }
+  t->tails.clear();
   if (t->ev_ready) cudaEventDestroy(t->ev_ready);
   for (int a = 0; a < 3; a++) {
     if (t->ev_k0[a]) cudaEventDestroy(t->ev_k0[a]);
-    if (t->ev_k1[a]) cudaEventDestroy(t->ev_k1[a]);
   }
 }
 
@@ -537,7 +570,15 @@ int th_init_staged(const int* gpu_ids, int n_gpus, size_t ring_bytes_per_gpu, si
       return rc;
     }
   }
+  if (const char* e = getenv("TRITONHASH_TICKET_TIMING")) c->timing = atoi(e) != 0;
   *out = c;
+  return TH_OK;
+}
+
+int th_set_ticket_timing(th_ctx* c, int on) {
+  if (!c) return TH_EINVAL;
+  std::lock_guard<std::mutex> lk(c->mu);
+  c->timing = on != 0;
   return TH_OK;
 }
 
@@ -649,6 +690,9 @@ static int submit_common(th_ctx* c, int gpu, Slot* slot, const void* d_base_user
   if (slot) t->slot_id = slot->id;
   rc = enqueue(c, g, t, d_base, slot, msgs, n, mask, t->has_expected ? expected : nullptr);
   if (rc != TH_OK) {
+    // items launched before the failure may still reference the ticket from their host callbacks
+    t->cb = nullptr;
+    cudaDeviceSynchronize();
     free_ticket_events(t);
     put_job(g, jb);
     delete t;
@@ -691,9 +735,12 @@ int th_submit_device(th_ctx* c, int gpu, const void* d_base, const th_msg* msgs,
 static int wait_locked(th_ctx* c, Ticket* t) {
   if (!t->finished) {
     cudaSetDevice(c->gpus[(size_t)t->gpu].dev);
-    cudaError_t e = cudaEventSynchronize(t->ev_done);
+    cudaError_t e = ticket_poll(t, true);
     t->finished = true;
     if (e != cudaSuccess) t->status = cuda_fail(c, e, "cudaEventSynchronize(ticket)");
+  }
+  if (!t->timed && t->status == TH_OK && t->ev_k0[0] == nullptr && t->ev_k0[1] == nullptr && t->ev_k0[2] == nullptr) {
+    t->timed = true;  // submitted with ticket timing off: times stay -1
   }
   if (!t->timed && t->status == TH_OK) {
     Gpu& g = c->gpus[(size_t)t->gpu];
@@ -701,9 +748,11 @@ static int wait_locked(th_ctx* c, Ticket* t) {
     if (t->ev_ready && cudaEventElapsedTime(&ms, g.ev_epoch, t->ev_ready) == cudaSuccess) t->times_ms[0] = ms;
     for (int a = 0; a < 3; a++) {
       if (!t->ev_k0[a]) continue;
-      if (cudaEventElapsedTime(&ms, t->ev_k0[a], t->ev_k1[a]) == cudaSuccess) g.st.kernel_ms += ms;
       if (cudaEventElapsedTime(&ms, g.ev_epoch, t->ev_k0[a]) == cudaSuccess) t->times_ms[1 + 2 * a] = ms;
-      if (cudaEventElapsedTime(&ms, g.ev_epoch, t->ev_k1[a]) == cudaSuccess) t->times_ms[2 + 2 * a] = ms;
+      for (auto& tl : t->tails)  // a digest ends when the last of its launch items does
+        if (tl.alg == a && tl.k_end && cudaEventElapsedTime(&ms, g.ev_epoch, tl.k_end) == cudaSuccess)
+          t->times_ms[2 + 2 * a] = std::max(t->times_ms[2 + 2 * a], (double)ms);
+      if (t->times_ms[1 + 2 * a] >= 0 && t->times_ms[2 + 2 * a] >= 0) g.st.kernel_ms += t->times_ms[2 + 2 * a] - t->times_ms[1 + 2 * a];
     }
     t->timed = true;
   }

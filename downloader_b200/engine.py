@@ -106,6 +106,11 @@ class Engine:
         check(rc, "th_submit_device", self._ctx)
         return t.value
 
+    def set_timing(self, on: bool) -> None:
+        """Per-ticket device timeline + stats()['kernel_ms'] for later submits (th_set_ticket_timing; a diagnostic:
+        it limits the library to 30 concurrent digest streams)."""
+        check(self._L.th_set_ticket_timing(self._ctx, 1 if on else 0), "th_set_ticket_timing", self._ctx)
+
     def timing(self, ticket: int) -> list:
         """[ready, sha1 start, sha1 end, md5 start, md5 end, sha256 start, sha256 end] in ms since th_init."""
         out = (C.c_double * 7)()

@@ -61,7 +61,7 @@ typedef struct th_stats {
   uint64_t h2d_bytes;   /* bytes copied host -> device (payload + descriptors) */
   uint64_t d2h_bytes;   /* bytes copied device -> host (digests, ok words) */
   uint64_t submits;
-  double kernel_ms;     /* summed device time of digest kernels (from CUDA events) */
+  double kernel_ms;     /* summed device time of digest kernels (CUDA events; only while ticket timing is on) */
 } th_stats;
 
 /* Completion callback, delivered on a library (CUDA host-callback) thread — the N-API shim
@@ -114,8 +114,14 @@ int th_submit_device(th_ctx* ctx, int gpu, const void* d_base, const th_msg* msg
 
 /* Device-side timeline of a ticket in milliseconds since th_init (waits for the ticket; call before th_result):
  * ms7[0] inputs on the device; ms7[1], ms7[2] start / end of the SHA-1 kernel(s); [3], [4] MD5; [5], [6] SHA-256;
- * -1 where a digest was not requested.  Used to see copy / kernel overlap of the host path (tools/config4.py). */
+ * -1 where a digest was not requested, and everywhere for tickets submitted with ticket timing off (the default).
+ * Used to see copy / kernel overlap of the host path (tools/config4.py --timeline). */
 int th_ticket_timing(th_ctx* ctx, th_ticket ticket, double* ms7);
+/* Turns the per-ticket timeline (and th_stats.kernel_ms) on or off for later submits; off by default, or set by
+ * TRITONHASH_TICKET_TIMING=1 at th_init.  It is a diagnostic: a timing-enabled CUDA event recorded behind a kernel
+ * holds its hardware queue until the kernel ends, so with it on the library keeps to 30 digest streams (one
+ * queue each) instead of 120, and at most 30 long chains (large parts) run at once.  No counterpart in the reference. */
+int th_set_ticket_timing(th_ctx* ctx, int on);
 
 /* Blocks until the ticket's digests are in host memory. */
 int th_wait(th_ctx* ctx, th_ticket ticket);

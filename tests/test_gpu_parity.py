@@ -324,6 +324,7 @@ def test_etag_combine_vs_oracle(eng, kat):
 def test_ring_many_slots_in_flight_and_wrap(torch):
     from downloader_b200 import Engine
     with Engine([0], ring_bytes=8 << 20) as e:
+        e.set_timing(True)  # stats()['kernel_ms'] is only kept with ticket timing on
         ln = 1 << 20
         tickets = []
         for k in range(20):  # 20 MiB through an 8 MiB ring: forces wrap + waits on the oldest slot
@@ -454,16 +455,28 @@ def test_messages_longer_than_512_mib_and_2_gib(torch, L):
 
 def test_ticket_timing_is_a_consistent_device_timeline(eng):
     """th_ticket_timing: inputs ready <= kernel start <= kernel end for requested digests, -1 for the others."""
-    import ctypes as C
     ln = 1 << 20
+    offs, lens = np.arange(4, dtype=np.uint64) * ln, np.full(4, ln, np.uint64)
+    try:
+        eng.set_timing(True)
+        slot, view = eng.ring_acquire(4 * ln)
+        view[:] = 7
+        k0 = eng.stats()["kernel_ms"]
+        t = eng.submit(slot, offs, lens, SHA1 | SHA256)
+        tm = eng.timing(t)
+        assert tm[0] >= 0 and tm[0] <= tm[1] <= tm[2] and tm[0] <= tm[5] <= tm[6]
+        assert tm[3] == -1 and tm[4] == -1
+        r = eng.result(t, 4, SHA1 | SHA256)
+        assert r[SHA1][0].tobytes() == hashlib.sha1(bytes([7]) * ln).digest()
+        assert eng.stats()["kernel_ms"] > k0
+    finally:
+        eng.set_timing(False)
+    # the default: no timing events on the streams, every entry -1, digests unaffected
     slot, view = eng.ring_acquire(4 * ln)
-    view[:] = 7
-    t = eng.submit(slot, np.arange(4, dtype=np.uint64) * ln, np.full(4, ln, np.uint64), SHA1 | SHA256)
-    tm = eng.timing(t)
-    assert tm[0] >= 0 and tm[0] <= tm[1] <= tm[2] and tm[0] <= tm[5] <= tm[6]
-    assert tm[3] == -1 and tm[4] == -1
-    r = eng.result(t, 4, SHA1 | SHA256)
-    assert r[SHA1][0].tobytes() == hashlib.sha1(bytes([7]) * ln).digest()
+    view[:] = 9
+    t = eng.submit(slot, offs, lens, MD5)
+    assert eng.timing(t) == [-1.0] * 7
+    assert eng.result(t, 4, MD5)[MD5][3].tobytes() == hashlib.md5(bytes([9]) * ln).digest()
 
 
 def test_few_large_ragged_messages_take_lone_launches(eng):

@@ -32,6 +32,7 @@ def main():
     ap.add_argument("--ring-gib", type=int, default=32)
     ap.add_argument("--slot-mib", type=int, default=1024)
     ap.add_argument("--device-gib", type=int, default=0, help="device staging ring (0 = same as the pinned ring)")
+    ap.add_argument("--timeline", action="store_true", help="per-ticket device timeline (th_set_ticket_timing: limits the run to 30 digest streams)")
     ap.add_argument("--files", type=int, default=10)
     ap.add_argument("--scale", type=float, default=1.0, help="scale file sizes (1.0 = 4..40 GiB)")
     a = ap.parse_args()
@@ -50,6 +51,7 @@ def main():
     win = pat.repeat(slot_bytes // PERIOD)
     n_dev_slots = max(n_slots, (a.device_gib * GiB) // slot_bytes)
     eng = Engine([0], ring_bytes=n_slots * slot_bytes, device_bytes=n_dev_slots * slot_bytes)
+    eng.set_timing(a.timeline)
     held = []
     for _ in range(n_slots):  # every slot gets the same window; contents persist across re-acquisition
         sid, view = eng.ring_acquire(slot_bytes)

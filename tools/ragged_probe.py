@@ -32,6 +32,7 @@ def main():
     L = _capi.lib()
     torch.cuda.set_device(0)
     eng = Engine([0], ring_bytes=1 << 20)
+    eng.set_timing(True)
     for name, lens in dists.items():
         lens = lens.astype(np.uint64)
         offs = np.zeros(lens.size, np.uint64)
