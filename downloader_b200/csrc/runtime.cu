@@ -384,7 +384,7 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
         size_t peel = 0;
         if (use_order && !verify) {
           const uint64_t median = h_len[m + h_ord[m + rest / 2]];
-          const size_t peel_max = 8;
+          static const size_t peel_max = [] { const char* e = getenv("TRITONHASH_PEEL_MAX"); return (size_t)(e ? std::max(0, atoi(e)) : 8); }();
           while (peel < peel_max && peel + 32 < rest) {
             const uint64_t l = h_len[m + h_ord[m + peel]];
             if (l < (256u << 10) || l < 8 * median || l >= (1ull << 31)) break;

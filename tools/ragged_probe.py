@@ -32,7 +32,8 @@ def main():
     L = _capi.lib()
     torch.cuda.set_device(0)
     eng = Engine([0], ring_bytes=1 << 20)
-    eng.set_timing(True)
+    timed = os.environ.get("PROBE_TIMING", "1") != "0"  # 0: wall clock around submit..result, ticket timing off
+    eng.set_timing(timed)
     for name, lens in dists.items():
         lens = lens.astype(np.uint64)
         offs = np.zeros(lens.size, np.uint64)
@@ -50,7 +51,7 @@ def main():
                 host = h1 if host is None else min(host, h1)
                 tm = eng.timing(t)
                 eng.result(t, lens.size, alg)
-                ms = tm[IDX[alg] + 1] - tm[IDX[alg]]
+                ms = (tm[IDX[alg] + 1] - tm[IDX[alg]]) if timed else (time.perf_counter() - h0) * 1e3
                 best = ms if best is None else min(best, ms)
             print(json.dumps({"dist": name, "alg": NAME[alg], "n": int(lens.size), "GiB": round(int(lens.sum()) / 2**30, 2),
                               "ms": round(best, 3), "submit_host_ms": round(host * 1e3, 3), "GBps": round(int(lens.sum()) / best / 1e6, 1)}), flush=True)
