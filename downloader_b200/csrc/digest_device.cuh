@@ -103,7 +103,8 @@ struct Md5 {
                           : lop3<LUT_MD5I>(b, c, d);
     // m[G] + T[I] depends on nothing in the chain: one IMAD on the FMA pipe.  The rest stays on the ALU pipe
     // as IADD3 (a + mk + f) and LEA.HI (rotl + b): 3 ALU + 1 FMA instructions per step.  (All three adds as
-    // IMAD measured slower: the step's dependent chain got longer than three warps can hide.)
+    // IMAD measured slower: the step's dependent chain got longer than three warps can hide; moving only the
+    // a + mk + f sum to IMADs, LEA.HI kept, also measured slower: 3.9 vs 4.7 TB/s, with 12 or 16 warps per SM.)
     uint32_t akm = a + add_fma(m[G], T[I], one);
     a = b + rotl(akm + f, S[(R << 2) | (I & 3)]);
   }
