@@ -1,0 +1,71 @@
+#!/usr/bin/env python
+"""north_star's pass bar, ">= 70 % of the per-GPU hashing roofline on 16 MiB-part batches", needs enough parts for
+every sub-partition to have work: one chain + helper warp per 32 parts fills the chip at 296 groups = 9,472 parts =
+148 GiB, the largest 16 MiB-part batch one B200 (180 GB) holds.  Device-resident, each digest alone and MD5 + SHA-256
+together, CUDA events, 3 parts per digest checked against hashlib.  One JSON line per run."""
+import argparse
+import ctypes as C
+import hashlib
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+
+from downloader_b200 import _capi
+
+OPS = {"sha1": 613, "md5": 324, "sha256": 1400}
+DL = {"sha1": 20, "md5": 16, "sha256": 32}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--parts", type=int, default=9472)
+    ap.add_argument("--mib", type=int, default=16)
+    a = ap.parse_args()
+    L = _capi.lib()
+    n, ln = a.parts, a.mib << 20
+    data = torch.empty(n * ln, dtype=torch.uint8, device="cuda")
+    L.th_synth_fill(data.data_ptr(), 0, n, ln, ln, 5, None)
+    torch.cuda.synchronize()
+    outs = {k: torch.zeros(n * DL[k], dtype=torch.uint8, device="cuda") for k in DL}
+    side = torch.cuda.Stream()
+
+    def launch(alg, stream):
+        sp = C.c_void_p(stream.cuda_stream)
+        if alg == "sha1":
+            return L.th_sha1_batch(data.data_ptr(), None, None, None, ln, ln, n, outs[alg].data_ptr(), None, None, sp)
+        fn = L.th_md5_batch if alg == "md5" else L.th_sha256_batch
+        return fn(data.data_ptr(), None, None, None, ln, ln, n, outs[alg].data_ptr(), sp)
+
+    cur = torch.cuda.current_stream()
+    for algs in (["sha1"], ["md5"], ["sha256"], ["md5", "sha256"]):
+        best = None
+        for _ in range(2):
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(cur)
+            side.wait_stream(cur)
+            assert launch(algs[0], cur) == 0
+            if len(algs) > 1:
+                assert launch(algs[1], side) == 0
+                cur.wait_stream(side)
+            e1.record(cur)
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1)
+            best = ms if best is None else min(best, ms)
+        for alg in algs:
+            for i in (0, n // 2, n - 1):
+                ref = getattr(hashlib, alg)(data[i * ln:(i + 1) * ln].cpu().numpy().tobytes()).digest()
+                assert outs[alg][i * DL[alg]:(i + 1) * DL[alg]].cpu().numpy().tobytes() == ref, (alg, i)
+        ops = sum(OPS[k] for k in algs) / 64.0
+        roof = 148 * 64 * 1.965e9 / ops / 1e9
+        gbps = n * ln / best / 1e6
+        print(json.dumps({"algs": "+".join(algs), "parts": n, "part_MiB": a.mib, "GiB": n * ln >> 30, "ms": round(best, 1),
+                          "GBps": round(gbps, 1), "int_roofline_GBps": round(roof, 1), "frac": round(gbps / roof, 3),
+                          "kernel": _capi.plan({"sha1": 1, "md5": 2, "sha256": 4}[algs[-1]], ln, ln, n).split(":")[0]}), flush=True)
+
+
+if __name__ == "__main__":
+    main()
