@@ -608,9 +608,9 @@ struct Assist<Sha256> {
     (void)one;
   }
   // The 64 rounds of one block on pre-expanded W+K read from `src` (this lane's 16-byte column).
-  // A warp alone on its sub-partition issues about one instruction every two clocks whatever the pipe
-  // (measured: IMAD adds were no faster), so what counts here is the instruction count: plain adds that
-  // ptxas packs into IADD3 — 14 instructions per round instead of 16.
+  // A warp alone on its sub-partition issues about one instruction every two clocks whatever the pipe, so both
+  // the instruction count and the e -> S1 -> e dependence matter: the 14-instruction form (en = d + t1) measured
+  // 262 ms per 16 MiB part, this 15-instruction form with en computed beside t1 247 ms.
   __device__ static __forceinline__ void rounds(uint32_t* h, const uint4* src, uint32_t one) {
     uint32_t a = h[0], b = h[1], c = h[2], d = h[3], e = h[4], f = h[5], g = h[6], hh = h[7];
 #pragma unroll
