@@ -1,5 +1,6 @@
-// tritonhash_napi.cc — N-API binding of include/tritonhash.h.  WRITTEN, NOT COMPILED HERE: the image has no
-// node_api.h and no Node.js (js/README.md).  One th_ctx per process; every call that touches the GPU is
+// tritonhash_napi.cc — N-API binding of include/tritonhash.h.  WRITTEN, NOT RUN HERE: the image has no
+// node_api.h and no Node.js (js/README.md); a CPU test type-checks it against N-API's documented prototypes
+// (tests/stubs/node_api.h) and links it against libtritonhash.so.  One th_ctx per process; every call that touches the GPU is
 // asynchronous: th_submit enqueues, the library's completion callback (a CUDA host-callback thread) hops to
 // the JS thread through a napi_threadsafe_function, and th_result fills the Buffers the Promise resolves with.
 #include <node_api.h>

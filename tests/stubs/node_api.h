@@ -1,0 +1,65 @@
+/* Test infrastructure: self-declared prototypes of the N-API calls js/addon/tritonhash_napi.cc uses, restated from
+ * Node's documented C API (n-api.md) so that the shim can at least be type-checked (`g++ -fsyntax-only`) on an
+ * image that has no Node headers.  Not shipped, not linked: the real build uses Node's own <node_api.h>. */
+#ifndef TESTS_STUBS_NODE_API_H
+#define TESTS_STUBS_NODE_API_H
+#include <stdbool.h>
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+typedef struct napi_env__* napi_env;
+typedef struct napi_value__* napi_value;
+typedef struct napi_ref__* napi_ref;
+typedef struct napi_deferred__* napi_deferred;
+typedef struct napi_callback_info__* napi_callback_info;
+typedef struct napi_threadsafe_function__* napi_threadsafe_function;
+typedef enum { napi_ok, napi_invalid_arg, napi_object_expected, napi_generic_failure, napi_pending_exception } napi_status;
+typedef napi_value (*napi_callback)(napi_env env, napi_callback_info info);
+typedef void (*napi_finalize)(napi_env env, void* finalize_data, void* finalize_hint);
+typedef void (*napi_threadsafe_function_call_js)(napi_env env, napi_value js_callback, void* context, void* data);
+typedef enum { napi_tsfn_release, napi_tsfn_abort } napi_threadsafe_function_release_mode;
+typedef enum { napi_tsfn_nonblocking, napi_tsfn_blocking } napi_threadsafe_function_call_mode;
+#define NAPI_AUTO_LENGTH SIZE_MAX
+napi_status napi_get_cb_info(napi_env env, napi_callback_info cbinfo, size_t* argc, napi_value* argv, napi_value* this_arg, void** data);
+napi_status napi_get_array_length(napi_env env, napi_value value, uint32_t* result);
+napi_status napi_get_element(napi_env env, napi_value object, uint32_t index, napi_value* result);
+napi_status napi_get_value_int32(napi_env env, napi_value value, int32_t* result);
+napi_status napi_get_value_uint32(napi_env env, napi_value value, uint32_t* result);
+napi_status napi_get_value_double(napi_env env, napi_value value, double* result);
+napi_status napi_get_value_bigint_uint64(napi_env env, napi_value value, uint64_t* result, bool* lossless);
+napi_status napi_get_undefined(napi_env env, napi_value* result);
+napi_status napi_get_named_property(napi_env env, napi_value object, const char* utf8name, napi_value* result);
+napi_status napi_set_named_property(napi_env env, napi_value object, const char* utf8name, napi_value value);
+napi_status napi_get_buffer_info(napi_env env, napi_value value, void** data, size_t* length);
+napi_status napi_is_buffer(napi_env env, napi_value value, bool* result);
+napi_status napi_create_uint32(napi_env env, uint32_t value, napi_value* result);
+napi_status napi_create_double(napi_env env, double value, napi_value* result);
+napi_status napi_create_object(napi_env env, napi_value* result);
+napi_status napi_create_string_utf8(napi_env env, const char* str, size_t length, napi_value* result);
+napi_status napi_create_error(napi_env env, napi_value code, napi_value msg, napi_value* result);
+napi_status napi_create_bigint_uint64(napi_env env, uint64_t value, napi_value* result);
+napi_status napi_create_buffer(napi_env env, size_t length, void** data, napi_value* result);
+napi_status napi_create_external_buffer(napi_env env, size_t length, void* data, napi_finalize finalize_cb, void* finalize_hint, napi_value* result);
+napi_status napi_create_function(napi_env env, const char* utf8name, size_t length, napi_callback cb, void* data, napi_value* result);
+napi_status napi_create_promise(napi_env env, napi_deferred* deferred, napi_value* promise);
+napi_status napi_resolve_deferred(napi_env env, napi_deferred deferred, napi_value resolution);
+napi_status napi_reject_deferred(napi_env env, napi_deferred deferred, napi_value rejection);
+napi_status napi_throw_error(napi_env env, const char* code, const char* msg);
+napi_status napi_throw_type_error(napi_env env, const char* code, const char* msg);
+napi_status napi_throw_range_error(napi_env env, const char* code, const char* msg);
+napi_status napi_delete_reference(napi_env env, napi_ref ref);
+napi_status napi_create_threadsafe_function(napi_env env, napi_value func, napi_value async_resource, napi_value async_resource_name,
+                                            size_t max_queue_size, size_t initial_thread_count, void* thread_finalize_data,
+                                            napi_finalize thread_finalize_cb, void* context, napi_threadsafe_function_call_js call_js_cb,
+                                            napi_threadsafe_function* result);
+napi_status napi_call_threadsafe_function(napi_threadsafe_function func, void* data, napi_threadsafe_function_call_mode is_blocking);
+napi_status napi_release_threadsafe_function(napi_threadsafe_function func, napi_threadsafe_function_release_mode mode);
+#ifdef __cplusplus
+}
+#define NAPI_MODULE_INIT() extern "C" napi_value napi_register_module_v1(napi_env env, napi_value exports)
+#else
+#define NAPI_MODULE_INIT() napi_value napi_register_module_v1(napi_env env, napi_value exports)
+#endif
+#endif

@@ -70,3 +70,29 @@ def test_init_fails_loudly_without_gpu():
     with pytest.raises(downloader_b200.TritonHashError) as ei:
         downloader_b200.Engine()
     assert ei.value.code == -2
+
+
+def test_napi_shim_type_checks_and_links_against_the_c_abi(tmp_path):
+    """js/addon/tritonhash_napi.cc cannot run here (no Node), but it must at least compile against N-API's documented
+    prototypes (tests/stubs/node_api.h) and resolve every th_* symbol it uses in libtritonhash.so."""
+    import shutil
+    import subprocess
+    if not shutil.which("g++"):
+        pytest.skip("g++ not available")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib = os.path.join(root, "downloader_b200", "libtritonhash.so")
+    if not os.path.exists(lib):
+        pytest.skip("libtritonhash.so not built")
+    out = tmp_path / "tritonhash.node"
+    cmd = ["g++", "-std=c++17", "-Wall", "-Wextra", "-Werror", "-shared", "-fPIC", "-I", os.path.join(root, "tests", "stubs"),
+           "-I", os.path.join(root, "include"), os.path.join(root, "js", "addon", "tritonhash_napi.cc"), "-o", str(out),
+           "-L", os.path.dirname(lib), "-ltritonhash"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]
+    syms = subprocess.run(["nm", "-D", str(out)], capture_output=True, text=True).stdout
+    assert " T napi_register_module_v1" in syms
+    used = sorted({ln.split()[-1] for ln in syms.splitlines() if " U th_" in ln})
+    assert "th_init_staged" in used and "th_submit" in used and "th_result" in used
+    exported = subprocess.run(["nm", "-D", "--defined-only", lib], capture_output=True, text=True).stdout
+    for s in used:
+        assert f" T {s}" in exported, s
