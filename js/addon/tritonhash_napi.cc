@@ -1,6 +1,6 @@
-// tritonhash_napi.cc — N-API binding of include/tritonhash.h.  WRITTEN, NOT RUN HERE: the image has no
-// node_api.h and no Node.js (js/README.md); a CPU test type-checks it against N-API's documented prototypes
-// (tests/stubs/node_api.h) and links it against libtritonhash.so.  One th_ctx per process; every call that touches the GPU is
+// tritonhash_napi.cc — N-API binding of include/tritonhash.h.  The image has no node_api.h and no Node.js
+// (js/README.md): a CPU test type-checks it against N-API's documented prototypes (tests/stubs/node_api.h) and links
+// it against libtritonhash.so, and a GPU test executes it under a miniature N-API runtime (tests/napi_mock/).  One th_ctx per process; every call that touches the GPU is
 // asynchronous: th_submit enqueues, the library's completion callback (a CUDA host-callback thread) hops to
 // the JS thread through a napi_threadsafe_function, and th_result fills the Buffers the Promise resolves with.
 #include <node_api.h>
@@ -143,6 +143,21 @@ napi_value RingAcquire(napi_env env, napi_callback_info info) {
   return out;
 }
 
+// ringRelease(slot: bigint): gives back a slot that will not be submitted (the read that was to fill it failed)
+napi_value RingRelease(napi_env env, napi_callback_info info) {
+  size_t argc = 1;
+  napi_value argv[1];
+  NAPI_OK(napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr));
+  uint64_t slot = 0;
+  bool lossless = false;
+  NAPI_OK(napi_get_value_bigint_uint64(env, argv[0], &slot, &lossless));
+  int rc = th_ring_release(g_ctx, slot);
+  if (rc != TH_OK) return throw_th(env, rc, "ringRelease");
+  napi_value u;
+  napi_get_undefined(env, &u);
+  return u;
+}
+
 // hashBatch(algMask, slot: bigint, msgs: {offset,length}[], expectedSha1?: Buffer) -> Promise<{sha1?,md5?,sha256?,okBits?}>
 napi_value HashBatch(napi_env env, napi_callback_info info) {
   size_t argc = 4;
@@ -233,7 +248,7 @@ napi_value Shutdown(napi_env env, napi_callback_info) {
 }  // namespace
 
 NAPI_MODULE_INIT() {
-  const struct { const char* name; napi_callback fn; } fns[] = {{"init", Init}, {"ringAcquire", RingAcquire},
+  const struct { const char* name; napi_callback fn; } fns[] = {{"init", Init}, {"ringAcquire", RingAcquire}, {"ringRelease", RingRelease},
       {"hashBatch", HashBatch}, {"etagCombine", EtagCombine}, {"stats", Stats}, {"shutdown", Shutdown}};
   for (const auto& f : fns) {
     napi_value v;

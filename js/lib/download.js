@@ -33,11 +33,16 @@ async function verifyOnDisk (files, pieceLength, pieces /* Buffer n*20 */, gpu =
       const { slot, buffer } = th.ringAcquire(gpu, bytes)
       buffer.fill(0, 0, bytes)
       let pos = 0
-      for (let i = 0; i < files.length; i++) { // files laid end to end, as the torrent sees them
-        const lo = Math.max(start, pos)
-        const hi = Math.min(start + bytes, pos + files[i].length)
-        if (hi > lo && handles[i]) await handles[i].read(buffer, lo - start, hi - lo, lo - pos)
-        pos += files[i].length
+      try {
+        for (let i = 0; i < files.length; i++) { // files laid end to end, as the torrent sees them
+          const lo = Math.max(start, pos)
+          const hi = Math.min(start + bytes, pos + files[i].length)
+          if (hi > lo && handles[i]) await handles[i].read(buffer, lo - start, hi - lo, lo - pos)
+          pos += files[i].length
+        }
+      } catch (err) {
+        th.ringRelease(slot) // an unsubmitted slot would block the ring for good
+        throw err
       }
       const msgs = []
       for (let k = 0; k < count; k++) msgs.push({ offset: k * pieceLength, length: Math.min(pieceLength, total - (first + k) * pieceLength) })

@@ -33,6 +33,11 @@ function ringAcquire (gpu, bytes) {
   return addon.ringAcquire(gpu, bytes)
 }
 
+/** gives back a slot that will not be submitted (e.g. the read that was to fill it failed) */
+function ringRelease (slot) {
+  addon.ringRelease(slot)
+}
+
 /**
  * SHA-1 of every message of a slot; with `expected` (n x 20 raw bytes, info.pieces) also the verified
  * bitfield: bit i <=> webtorrent's `hash === this._hashes[i]`.
@@ -63,4 +68,4 @@ function multipartEtag (md5s) {
   return addon.etagCombine(md5s, [n]).toString('hex') + '-' + n
 }
 
-module.exports = { SHA1, MD5, SHA256, init, shutdown, ringAcquire, sha1Batch, partDigests, multipartEtag, stats: () => addon.stats() }
+module.exports = { SHA1, MD5, SHA256, init, shutdown, ringAcquire, ringRelease, sha1Batch, partDigests, multipartEtag, stats: () => addon.stats() }

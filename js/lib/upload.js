@@ -38,7 +38,12 @@ async function digestParts (file, size, partSize, gpu, slotBytes, mode) {
       const start = first * partSize
       const bytes = Math.min(count * partSize, size - start)
       const { slot, buffer } = th.ringAcquire(gpu, Math.max(bytes, 16))
-      if (bytes > 0) await fd.read(buffer, 0, bytes, start) // straight into pinned memory
+      try {
+        if (bytes > 0) await fd.read(buffer, 0, bytes, start) // straight into pinned memory
+      } catch (err) {
+        th.ringRelease(slot) // an unsubmitted slot would block the ring for good
+        throw err
+      }
       const msgs = []
       for (let k = 0; k < count; k++) msgs.push({ offset: k * partSize, length: Math.min(partSize, size - (first + k) * partSize) })
       const r = await th.partDigests(slot, msgs, { both: true, enableSHA256: mode.enableSHA256 })

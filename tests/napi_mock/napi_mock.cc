@@ -200,6 +200,11 @@ int main() {
   q = call(exports, "hashBatch", {num(1), acq2->props.at("slot"), num(3)});
   CHECK(q == nullptr && g_env.pending && g_env.code == "TypeError", "non-array msgs must throw a TypeError");
 
+  call(exports, "ringRelease", {acq2->props.at("slot")});  // the slot that was never submitted goes back to the ring
+  CHECK(!g_env.pending, g_env.message.c_str());
+  call(exports, "ringRelease", {acq2->props.at("slot")});
+  CHECK(g_env.pending && g_env.code == "ERRTRITONHASH", "releasing a slot twice must throw");
+
   napi_value st = call(exports, "stats", {});
   CHECK(st && st->props.at("submits")->num == 1 && st->props.at("messages")->num == 3 * n, "stats");
   call(exports, "shutdown", {});
