@@ -143,11 +143,15 @@ def _stream_messages(engine, src: _ConcatFiles, bounds: Sequence[Tuple[int, int]
         drain(in_flight - 1)
         slot, view = engine.ring_acquire(max(pos, 16), gpu)
         contiguous = all(bounds[k + 1][0] == bounds[k][1] and (bounds[k][1] - bounds[k][0]) % 16 == 0 for k in range(i, j - 1))
-        if contiguous:  # pieces / parts back to back: one sequential read for the whole slot
-            src.readinto(view[:bounds[j - 1][1] - bounds[i][0]], bounds[i][0])
-        else:
-            for k in range(i, j):
-                src.readinto(view[offs[k - i]:offs[k - i] + lens[k - i]], bounds[k][0])
+        try:
+            if contiguous:  # pieces / parts back to back: one sequential read for the whole slot
+                src.readinto(view[:bounds[j - 1][1] - bounds[i][0]], bounds[i][0])
+            else:
+                for k in range(i, j):
+                    src.readinto(view[offs[k - i]:offs[k - i] + lens[k - i]], bounds[k][0])
+        except BaseException:
+            engine.ring_release(slot)  # an unsubmitted slot would block the ring for good
+            raise
         exp = expected_sha1[i:j] if expected_sha1 is not None else None
         pending.append((engine.submit(slot, np.array(offs, np.uint64), np.array(lens, np.uint64), algs, exp), i, j - i))
         i = j
@@ -230,7 +234,11 @@ def hash_media_file(engine, path: str, piece_length: int, expected_sha1, part_ra
                 raise ValueError("part boundaries must be multiples of the piece length")
             drain(in_flight - 1)
             slot, view = engine.ring_acquire(max(end - start, 16), gpu)
-            src.readinto(view[:end - start], start)
+            try:
+                src.readinto(view[:end - start], start)
+            except BaseException:
+                engine.ring_release(slot)  # an unsubmitted slot would block the ring for good
+                raise
             p0, p1 = start // piece_length, -(-end // piece_length)
             offs = np.array([pb[i][0] - start for i in range(p0, p1)], np.uint64)
             lens = np.array([pb[i][1] - pb[i][0] for i in range(p0, p1)], np.uint64)
