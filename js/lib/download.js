@@ -17,6 +17,7 @@ const path = require('path')
 const th = require('./tritonhash')
 
 const STALL_MS = 240000
+const IN_FLIGHT = 4 // slots submitted and not yet collected
 
 /** Re-hash a download directory against info.pieces; returns the verified bitfield as boolean[] */
 async function verifyOnDisk (files, pieceLength, pieces /* Buffer n*20 */, gpu = 0, slotBytes = 256 * 1024 * 1024) {
@@ -25,6 +26,8 @@ async function verifyOnDisk (files, pieceLength, pieces /* Buffer n*20 */, gpu =
   const ok = new Array(nPieces).fill(false)
   const perSlot = Math.max(1, Math.floor(slotBytes / pieceLength))
   const handles = await Promise.all(files.map(f => fsp.open(f.path, 'r').catch(() => null)))
+  const pending = []
+  const collect = ({ r, first, count }) => { for (let k = 0; k < count; k++) ok[first + k] = r.ok[k] }
   try {
     for (let first = 0; first < nPieces; first += perSlot) {
       const count = Math.min(perSlot, nPieces - first)
@@ -46,9 +49,11 @@ async function verifyOnDisk (files, pieceLength, pieces /* Buffer n*20 */, gpu =
       }
       const msgs = []
       for (let k = 0; k < count; k++) msgs.push({ offset: k * pieceLength, length: Math.min(pieceLength, total - (first + k) * pieceLength) })
-      const r = await th.sha1Batch(slot, msgs, pieces.slice(first * 20, (first + count) * 20))
-      for (let k = 0; k < count; k++) ok[first + k] = r.ok[k]
+      // keep reading while the slot is hashed: digests are collected a few slots later
+      pending.push(th.sha1Batch(slot, msgs, pieces.slice(first * 20, (first + count) * 20)).then(r => ({ r, first, count })))
+      if (pending.length >= IN_FLIGHT) collect(await pending.shift())
     }
+    while (pending.length) collect(await pending.shift())
   } finally {
     await Promise.all(handles.map(h => h && h.close()))
   }
@@ -58,7 +63,7 @@ async function verifyOnDisk (files, pieceLength, pieces /* Buffer n*20 */, gpu =
 module.exports = async (config, emitter, logger) => {
   const downloadStage = config.downloadStageEnum
   const sourceName = config.sourceTypeName // (enumValue) => 'TORRENT' | 'HTTP' | 'FILE' | 'BUCKET'
-  th.init(config.gpus || [0], config.ringBytes || (1 << 30))
+  th.init(config.gpus || [0], config.ringBytes || (1 << 30), config.deviceRingBytes || 0) // device ring: 0 = same size as the pinned ring
 
   const methods = {
     torrent: async (uri, id, downloadPath) => {

@@ -18,6 +18,7 @@ const th = require('./tritonhash')
 
 const BUCKET = 'triton-staging'
 const MiB = 1024 * 1024
+const IN_FLIGHT = 8 // slots submitted and not yet collected (the device ring holds them; th_init_staged)
 
 function partSizeFor (size, base = 64 * MiB, override = false) {
   if (override) return base
@@ -30,6 +31,11 @@ async function digestParts (file, size, partSize, gpu, slotBytes, mode) {
   const fd = await fsp.open(file, 'r')
   const md5 = Buffer.alloc(Math.max(1, Math.ceil(size / partSize)) * 16)
   const perPart = []
+  const pending = []
+  const collect = ({ r, first }) => {
+    r.md5.copy(md5, first * 16)
+    for (let k = 0; k < r.digests.length; k++) perPart[first + k] = r.digests[k]
+  }
   try {
     const partsPerSlot = Math.max(1, Math.floor(slotBytes / partSize))
     const nParts = Math.max(1, Math.ceil(size / partSize))
@@ -46,10 +52,11 @@ async function digestParts (file, size, partSize, gpu, slotBytes, mode) {
       }
       const msgs = []
       for (let k = 0; k < count; k++) msgs.push({ offset: k * partSize, length: Math.min(partSize, size - (first + k) * partSize) })
-      const r = await th.partDigests(slot, msgs, { both: true, enableSHA256: mode.enableSHA256 })
-      r.md5.copy(md5, first * 16)
-      perPart.push(...r.digests)
+      // a slot's digests arrive one chain latency after its copy (0.25 s for 16 MiB parts): keep reading while they run
+      pending.push(th.partDigests(slot, msgs, { both: true, enableSHA256: mode.enableSHA256 }).then(r => ({ r, first })))
+      if (pending.length >= IN_FLIGHT) collect(await pending.shift())
     }
+    while (pending.length) collect(await pending.shift())
   } finally {
     await fd.close()
   }
@@ -60,7 +67,7 @@ module.exports = async (config, emitter, logger) => {
   const s3 = config.s3
   const mode = { enableSHA256: !config.anonymous && !config.useSSL }
   const downloadStage = config.downloadStageEnum
-  th.init(config.gpus || [0], config.ringBytes || (1 << 30))
+  th.init(config.gpus || [0], config.ringBytes || (1 << 30), config.deviceRingBytes || 0) // device ring: 0 = same size as the pinned ring
 
   return async job => {
     const { files, downloadPath } = job.lastStage
