@@ -72,6 +72,7 @@ def lib() -> C.CDLL:
     L.th_shutdown.argtypes = [vp]
     L.th_gpu_count.argtypes = [vp]
     L.th_ring_acquire.argtypes = [vp, i32, C.c_size_t, C.POINTER(vp), C.POINTER(u64)]
+    L.th_ring_try_acquire.argtypes = [vp, i32, C.c_size_t, C.POINTER(vp), C.POINTER(u64)]
     L.th_ring_release.argtypes = [vp, u64]
     L.th_submit.argtypes = [vp, u64, C.POINTER(ThMsg), C.c_size_t, u32, vp, DONE_CB, vp, C.POINTER(u64)]
     L.th_submit_device.argtypes = [vp, i32, vp, C.POINTER(ThMsg), C.c_size_t, u32, vp, DONE_CB, vp, C.POINTER(u64)]

@@ -611,7 +611,17 @@ int th_shutdown(th_ctx* c) {
 
 int th_gpu_count(const th_ctx* c) { return c ? (int)c->gpus.size() : TH_EINVAL; }
 
+static int ring_acquire(th_ctx* c, int gpu, size_t bytes, void** host_ptr, th_slot* slot, bool wait);
+
 int th_ring_acquire(th_ctx* c, int gpu, size_t bytes, void** host_ptr, th_slot* slot) {
+  return ring_acquire(c, gpu, bytes, host_ptr, slot, true);
+}
+
+int th_ring_try_acquire(th_ctx* c, int gpu, size_t bytes, void** host_ptr, th_slot* slot) {
+  return ring_acquire(c, gpu, bytes, host_ptr, slot, false);
+}
+
+static int ring_acquire(th_ctx* c, int gpu, size_t bytes, void** host_ptr, th_slot* slot, bool wait) {
   if (!c || !host_ptr || !slot || gpu < 0 || gpu >= (int)c->gpus.size() || bytes == 0) return TH_EINVAL;
   std::lock_guard<std::mutex> lk(c->mu);
   if (c->sticky) return c->sticky;
@@ -642,14 +652,14 @@ int th_ring_acquire(th_ctx* c, int gpu, size_t bytes, void** host_ptr, th_slot* 
       return TH_OK;
     }
     if (off == (size_t)-1) {  // pinned ring full: wait for the oldest outstanding H2D copy
-      if (!busy->submitted) return TH_EBUSY;
+      if (!busy->submitted || !wait) return TH_EBUSY;
       cudaError_t e = cudaEventSynchronize(busy->ev_copied);
       if (e != cudaSuccess) return cuda_fail(c, e, "cudaEventSynchronize(slot copy)");
       busy->host_free = true;
       continue;
     }
     // device ring full: wait for the oldest slot's tickets
-    if (!g.slots.front().submitted) return TH_EBUSY;
+    if (!g.slots.front().submitted || !wait) return TH_EBUSY;
     reap(c, g, true);
     if (c->sticky) return c->sticky;
   }

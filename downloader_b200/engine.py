@@ -58,10 +58,17 @@ class Engine:
             pass
 
     # -- ring -----------------------------------------------------------------------------------
-    def ring_acquire(self, nbytes: int, gpu: int = 0):
-        """-> (slot id, writable uint8 numpy view of the pinned slot)."""
+    def ring_acquire(self, nbytes: int, gpu: int = 0, wait: bool = True):
+        """-> (slot id, writable uint8 numpy view of the pinned slot).  wait=False never blocks: returns None when
+        the bytes do not fit right now (th_ring_try_acquire)."""
         ptr, slot = C.c_void_p(), C.c_uint64()
-        check(self._L.th_ring_acquire(self._ctx, gpu, nbytes, C.byref(ptr), C.byref(slot)), "th_ring_acquire", self._ctx)
+        if not wait:
+            rc = self._L.th_ring_try_acquire(self._ctx, gpu, nbytes, C.byref(ptr), C.byref(slot))
+            if rc == -6:  # TH_EBUSY
+                return None
+            check(rc, "th_ring_try_acquire", self._ctx)
+        else:
+            check(self._L.th_ring_acquire(self._ctx, gpu, nbytes, C.byref(ptr), C.byref(slot)), "th_ring_acquire", self._ctx)
         view = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), shape=(nbytes,))
         return slot.value, view
 

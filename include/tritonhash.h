@@ -91,6 +91,10 @@ int th_gpu_count(const th_ctx* ctx);
  * completed (TH_EBUSY instead if the slot it would wait for has not been submitted).  The pinned bytes return
  * to the ring when the slot's copy completes, the device bytes when all of its tickets have. */
 int th_ring_acquire(th_ctx* ctx, int gpu, size_t bytes, void** host_ptr, th_slot* slot);
+/* Same, but never waits: TH_EBUSY when the bytes do not fit right now.  For callers that must not block their
+ * thread — Node's event loop: the add-on returns null and the JS side awaits its oldest outstanding Promise
+ * before trying again.  No counterpart in the reference. */
+int th_ring_try_acquire(th_ctx* ctx, int gpu, size_t bytes, void** host_ptr, th_slot* slot);
 /* Drops a slot that was acquired but will not be submitted. */
 int th_ring_release(th_ctx* ctx, th_slot slot);
 

@@ -121,7 +121,7 @@ napi_value Init(napi_env env, napi_callback_info info) {
   return u;
 }
 
-// ringAcquire(gpu, bytes) -> { slot: bigint, buffer: Buffer over the pinned slot (fs.read target) }
+// ringAcquire(gpu, bytes) -> { slot: bigint, buffer: Buffer over the pinned slot (fs.read target) } | null (ring full)
 napi_value RingAcquire(napi_env env, napi_callback_info info) {
   size_t argc = 2;
   napi_value argv[2];
@@ -132,7 +132,13 @@ napi_value RingAcquire(napi_env env, napi_callback_info info) {
   NAPI_OK(napi_get_value_double(env, argv[1], &bytes));
   void* host = nullptr;
   th_slot slot = 0;
-  int rc = th_ring_acquire(g_ctx, gpu, static_cast<size_t>(bytes), &host, &slot);
+  // never block Node's event loop: when the ring is full the caller gets null and awaits its oldest Promise
+  int rc = th_ring_try_acquire(g_ctx, gpu, static_cast<size_t>(bytes), &host, &slot);
+  if (rc == TH_EBUSY) {
+    napi_value nul;
+    NAPI_OK(napi_get_null(env, &nul));
+    return nul;
+  }
   if (rc != TH_OK) return throw_th(env, rc, "ringAcquire");
   napi_value out, s, b;
   NAPI_OK(napi_create_object(env, &out));

@@ -33,7 +33,7 @@ async function verifyOnDisk (files, pieceLength, pieces /* Buffer n*20 */, gpu =
       const count = Math.min(perSlot, nPieces - first)
       const start = first * pieceLength
       const bytes = Math.min(count * pieceLength, total - start)
-      const { slot, buffer } = th.ringAcquire(gpu, bytes)
+      const { slot, buffer } = await th.ringAcquire(gpu, bytes, pending, collect)
       buffer.fill(0, 0, bytes)
       let pos = 0
       try {

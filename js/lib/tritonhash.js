@@ -28,9 +28,17 @@ function shutdown () {
   started = false
 }
 
-/** pinned slot the caller fills, e.g. `await fd.read(buffer, 0, n, pos)` */
-function ringAcquire (gpu, bytes) {
-  return addon.ringAcquire(gpu, bytes)
+/**
+ * pinned slot the caller fills, e.g. `await fd.read(buffer, 0, n, pos)`.  Never blocks the event loop: while the
+ * ring is full it awaits the caller's oldest outstanding digest Promise (`pending`, shifted by the caller) and retries.
+ */
+async function ringAcquire (gpu, bytes, pending = [], collect = () => {}) {
+  for (;;) {
+    const r = addon.ringAcquire(gpu, bytes)
+    if (r) return r
+    if (pending.length) collect(await pending.shift())
+    else await new Promise(resolve => setImmediate(resolve)) // slots of other callers: let their completions run
+  }
 }
 
 /** gives back a slot that will not be submitted (e.g. the read that was to fill it failed) */

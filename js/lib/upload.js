@@ -43,7 +43,7 @@ async function digestParts (file, size, partSize, gpu, slotBytes, mode) {
       const count = Math.min(partsPerSlot, nParts - first)
       const start = first * partSize
       const bytes = Math.min(count * partSize, size - start)
-      const { slot, buffer } = th.ringAcquire(gpu, Math.max(bytes, 16))
+      const { slot, buffer } = await th.ringAcquire(gpu, Math.max(bytes, 16), pending, collect)
       try {
         if (bytes > 0) await fd.read(buffer, 0, bytes, start) // straight into pinned memory
       } catch (err) {

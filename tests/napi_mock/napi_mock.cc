@@ -19,7 +19,7 @@
 #include <vector>
 
 struct napi_value__ {
-  enum T { UNDEF, NUM, BIGINT, STR, OBJ, ARR, BUF, FUNC, ERR, PROMISE } t = UNDEF;
+  enum T { UNDEF, NUL, NUM, BIGINT, STR, OBJ, ARR, BUF, FUNC, ERR, PROMISE } t = UNDEF;
   double num = 0;
   uint64_t big = 0;
   std::string str;
@@ -60,6 +60,7 @@ napi_status napi_get_value_uint32(napi_env, napi_value v, uint32_t* r) { if (v->
 napi_status napi_get_value_double(napi_env, napi_value v, double* r) { if (v->t != napi_value__::NUM) return napi_invalid_arg; *r = v->num; return napi_ok; }
 napi_status napi_get_value_bigint_uint64(napi_env, napi_value v, uint64_t* r, bool* lossless) { if (v->t != napi_value__::BIGINT) return napi_invalid_arg; *r = v->big; *lossless = true; return napi_ok; }
 napi_status napi_get_undefined(napi_env, napi_value* r) { *r = mk(napi_value__::UNDEF); return napi_ok; }
+napi_status napi_get_null(napi_env, napi_value* r) { *r = mk(napi_value__::NUL); return napi_ok; }
 napi_status napi_get_named_property(napi_env, napi_value o, const char* k, napi_value* r) {
   if (o->t != napi_value__::OBJ) return napi_object_expected;
   auto it = o->props.find(k); *r = it == o->props.end() ? mk(napi_value__::UNDEF) : it->second; return napi_ok;
@@ -200,6 +201,9 @@ int main() {
   q = call(exports, "hashBatch", {num(1), acq2->props.at("slot"), num(3)});
   CHECK(q == nullptr && g_env.pending && g_env.code == "TypeError", "non-array msgs must throw a TypeError");
 
+  // a full ring is not an error and must not block the event loop: ringAcquire returns null
+  napi_value big = call(exports, "ringAcquire", {num(0), num((double)((64 << 20) - 2048))});
+  CHECK(!g_env.pending && big && big->t == napi_value__::NUL, "ringAcquire on a full ring must return null");
   call(exports, "ringRelease", {acq2->props.at("slot")});  // the slot that was never submitted goes back to the ring
   CHECK(!g_env.pending, g_env.message.c_str());
   call(exports, "ringRelease", {acq2->props.at("slot")});

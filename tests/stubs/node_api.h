@@ -30,6 +30,7 @@ napi_status napi_get_value_uint32(napi_env env, napi_value value, uint32_t* resu
 napi_status napi_get_value_double(napi_env env, napi_value value, double* result);
 napi_status napi_get_value_bigint_uint64(napi_env env, napi_value value, uint64_t* result, bool* lossless);
 napi_status napi_get_undefined(napi_env env, napi_value* result);
+napi_status napi_get_null(napi_env env, napi_value* result);
 napi_status napi_get_named_property(napi_env env, napi_value object, const char* utf8name, napi_value* result);
 napi_status napi_set_named_property(napi_env env, napi_value object, const char* utf8name, napi_value value);
 napi_status napi_get_buffer_info(napi_env env, napi_value value, void** data, size_t* length);

@@ -589,6 +589,7 @@ def test_device_ring_smaller_than_the_stream_blocks_and_recovers(torch):
         with pytest.raises(TritonHashError) as ei:
             e.ring_acquire(ln)  # device ring full and slot `a` was never submitted
         assert ei.value.code == -6
+        assert e.ring_acquire(ln, wait=False) is None  # th_ring_try_acquire: same condition, reported without waiting
         e.ring_release(a)
         vb[:] = 7
         t = e.submit(b, offs, lens, MD5)
