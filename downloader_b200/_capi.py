@@ -30,7 +30,7 @@ class ThMsg(C.Structure):
 class ThStats(C.Structure):
     _fields_ = [("messages", C.c_uint64), ("bytes", C.c_uint64), ("launches", C.c_uint64),
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("submits", C.c_uint64),
-                ("kernel_ms", C.c_double)]
+                ("kernel_ms", C.c_double), ("overflow_allocs", C.c_uint64)]
 
 
 DONE_CB = C.CFUNCTYPE(None, C.c_void_p, C.c_uint64, C.c_int)
@@ -77,6 +77,7 @@ def lib() -> C.CDLL:
     L.th_submit.argtypes = [vp, u64, C.POINTER(ThMsg), C.c_size_t, u32, vp, DONE_CB, vp, C.POINTER(u64)]
     L.th_submit_device.argtypes = [vp, i32, vp, C.POINTER(ThMsg), C.c_size_t, u32, vp, DONE_CB, vp, C.POINTER(u64)]
     L.th_wait.argtypes = [vp, u64]
+    L.th_poll.argtypes = [vp, u64]
     L.th_ticket_timing.argtypes = [vp, u64, C.POINTER(C.c_double)]
     L.th_result.argtypes = [vp, u64, vp, vp, vp, vp]
     L.th_etag_combine.argtypes = [vp, i32, vp, vp, C.c_size_t, vp]

@@ -746,8 +746,15 @@ int th_digest_ragged_static(uint32_t alg, const void* d_base, const uint64_t* d_
   if (th::alg_index(alg) < 0 || !d_out || !d_offsets || !d_lengths) return TH_EINVAL;
   if (n > TH_STATIC_MAX_MSGS) return TH_ETOOBIG;  // the built-in scratch holds TH_STATIC_MAX_MSGS slots
   if (n == 0) return TH_OK;
+  // everything the host can check is checked before the first enqueue, so a refused call leaves the stream untouched
+  if (!d_base) return TH_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(d_base) & 15) != 0) return TH_EALIGN;
   th::StaticScratch* s = nullptr;
-  if (th::static_scratch_ptr(&s) != cudaSuccess) return TH_ECUDA;  // first call on this device: symbol lookup
+  // First call on this device: the symbol lookup (like any first launch) makes the driver load this library's
+  // device code and place the scratch array in device memory.  That is the one moment the call can run out of memory.
+  const cudaError_t e0 = th::static_scratch_ptr(&s);
+  if (e0 == cudaErrorMemoryAllocation) { cudaGetLastError(); return TH_ENOMEM; }
+  if (e0 != cudaSuccess) return TH_ECUDA;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   // the array still holds the previous call's counters: they must start from zero
   if (cudaMemsetAsync(s, 0, 2 * th::kLenClasses * sizeof(uint32_t), st) != cudaSuccess) return TH_ECUDA;
@@ -756,7 +763,9 @@ int th_digest_ragged_static(uint32_t alg, const void* d_base, const uint64_t* d_
   const uint32_t blocks = (n + 255u) / 256u;
   th::class_count_kernel<<<blocks, 256, 0, st>>>(d_lengths, n, s);
   th::class_place_kernel<<<blocks, 256, 0, st>>>(d_lengths, n, s);
-  if (cudaGetLastError() != cudaSuccess) return TH_ECUDA;
+  const cudaError_t e1 = cudaGetLastError();
+  if (e1 == cudaErrorMemoryAllocation) return TH_ENOMEM;
+  if (e1 != cudaSuccess) return TH_ECUDA;
   return th::launch_digest(alg, d_base, d_offsets, d_lengths, s->order, 0, 0, n, d_out,
                            verify ? d_expected20 : nullptr, verify ? d_ok_bits : nullptr, stream);
 }

@@ -8,18 +8,27 @@
 // cudaMemcpyAsync D2H of the 16..32-byte digests.  Everything is enqueued by th_submit and never
 // blocks; rings are double-buffered simply by holding two or more slots in flight.
 //
+// Threading: every GPU of a context has its own lock, rings, streams, job buffers, tickets and
+// statistics, so threads feeding different GPUs never meet; ticket and slot ids carry their GPU's index.  One
+// library thread per context (the "completer") delivers completion callbacks with no lock held and doubles as
+// the watchdog that reports a faulted device to callers who would otherwise wait for a callback for ever.
+//
 // There is no CPU fallback: every path ends in a kernel of kernels.cu or fails with an error code.
 #include <algorithm>
 #include <atomic>
+#include <chrono>
+#include <condition_variable>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <deque>
 #include <map>
+#include <memory>
 #include <mutex>
 #include <numeric>
 #include <string>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -30,6 +39,8 @@
 namespace {
 
 constexpr size_t kRingAlign = 256;
+constexpr int kGpuBits = 6;  // ids = (sequence << 6) | index of the GPU in its context
+constexpr int kMaxGpus = 1 << kGpuBits;
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
@@ -82,12 +93,14 @@ struct Ticket {
   // 0.25..1 s chain also parks every stream that shares its hardware queue (120 streams share 32 queues).
   struct Tail { cudaEvent_t k_end; cudaEvent_t done; int alg; };
   std::vector<Tail> tails;
-  std::atomic<int> cb_left{0};  // launch items that have not reached their host callback yet
-  cudaEvent_t ev_ready = nullptr;  // inputs (payload + descriptors) on the device; timing-enabled
+  std::atomic<int> cb_left{0};  // launch items that have not reached their host function yet
+  cudaEvent_t ev_ready = nullptr;  // inputs (payload + descriptors) on the device; timing-enabled when timing is on
+  bool ev_ready_pooled = false;
   double times_ms[7] = {-1, -1, -1, -1, -1, -1, -1};  // since th_init: ready, then start / end per digest
   cudaEvent_t ev_k0[3] = {nullptr, nullptr, nullptr};  // start of each digest's first launch item
   th_done_cb cb = nullptr;
   void* user = nullptr;
+  int cb_state = 0;            // 0 not delivered yet, 1 running on the completer thread, 2 returned
   struct th_ctx* ctx = nullptr;
 };
 
@@ -105,11 +118,14 @@ struct StreamSet {
 
 struct Gpu {
   int dev = -1;
-  cudaStream_t s_copy = nullptr, s_misc = nullptr;  // H2D copies; synchronous odd jobs (ETag combine)
+  int index = 0;               // position in th_ctx::gpus (the low bits of this GPU's ticket and slot ids)
+  std::mutex mu;               // guards everything below; threads feeding different GPUs never contend
+  std::unordered_map<uint64_t, Ticket*> tickets;
+  cudaStream_t s_copy = nullptr, s_misc = nullptr;  // H2D copies; odd jobs (ETag combine)
   cudaEvent_t ev_epoch = nullptr;                   // recorded in th_init: origin of th_ticket_timing
   StreamSet sets[kMaxStreamSets];
   int n_sets = kStreamSets;     // TRITONHASH_STREAM_SETS (1..40) overrides
-  uint64_t next_stream[3] = {0, 0, 0};  // each digest rotates over its own 10 streams, whatever mix of submits arrives
+  uint64_t next_stream[3] = {0, 0, 0};  // each digest rotates over its own streams, whatever mix of submits arrives
   // Two FIFO rings with separate lifetimes: a slot's pinned bytes are needed only until its H2D copy has run,
   // its device bytes until the last kernel reading them has finished.  A chain over a 16 MiB part runs for
   // ~0.25 s, several times longer than the copy of the whole slot, so the device ring may be made (much) larger
@@ -123,35 +139,49 @@ struct Gpu {
   std::vector<JobBuf*> free_jobs;
   // Staging arena: one pinned + one device block allocated in th_init, carved first-fit into job buffers.
   // cudaMalloc / cudaHostAlloc on the submit path would wait for every running kernel (they synchronise the
-  // device), which serialises exactly the long kernels that must overlap; they remain only as the overflow path.
+  // device), which serialises exactly the long kernels that must overlap; they remain only as the overflow path
+  // (counted in th_stats.overflow_allocs).
   uint8_t* arena_h = nullptr;
   uint8_t* arena_d = nullptr;
   size_t arena_bytes = 0;
   std::map<size_t, size_t> arena_free;  // offset -> length, coalesced
+  std::vector<cudaEvent_t> ev_pool;     // untimed events, recycled: a submit records one per launch item
   th_stats st{};
 };
 
 }  // namespace
 
 struct th_ctx {
-  std::vector<Gpu> gpus;
-  std::mutex mu;
-  std::unordered_map<uint64_t, Ticket*> tickets;
-  uint64_t next_id = 1;
-  std::string last_error;
-  int sticky = TH_OK;
+  std::vector<std::unique_ptr<Gpu>> gpus;
+  std::atomic<uint64_t> next_seq{1};
+  std::mutex err_mu;
+  char last_error[512] = {0};
+  std::atomic<int> sticky{TH_OK};
   // Per-ticket device timeline (th_ticket_timing, th_stats.kernel_ms).  OFF by default: a timing-enabled event
   // recorded behind a kernel holds its hardware queue until the kernel ends (measured, tools/microbench/queues.cu:
   // 128 streams of 50 ms kernels take 50 ms with plain events and 200 ms with timing events), which caps the
   // long chains of large parts at 32 at a time.  When on, the rotation keeps to 10 stream sets (one queue each).
-  bool timing = false;
+  std::atomic<bool> timing{false};
+  // Completion delivery.  The CUDA host function of a ticket's last launch item only queues the ticket id here;
+  // the completer thread calls the user's callback with no library lock held, so the callback may call th_*.
+  std::thread completer;
+  std::thread::id completer_id;
+  std::mutex cq_mu;
+  std::condition_variable cq_cv;     // work for the completer
+  std::condition_variable cb_cv;     // a callback has returned (th_result waits for its ticket's)
+  std::deque<uint64_t> cq_ready;
+  std::atomic<int> cb_outstanding{0};  // tickets submitted with a callback that has not been delivered
+  bool stop = false;
 };
 
 namespace {
 
 int cuda_fail(th_ctx* c, cudaError_t e, const char* what) {
-  c->last_error = std::string(what) + ": " + cudaGetErrorString(e);
-  c->sticky = TH_ECUDA;
+  {
+    std::lock_guard<std::mutex> lk(c->err_mu);
+    snprintf(c->last_error, sizeof(c->last_error), "%s: %s", what, cudaGetErrorString(e));
+  }
+  c->sticky.store(TH_ECUDA);
   return TH_ECUDA;
 }
 #define CU(ctx, call)                                             \
@@ -159,6 +189,23 @@ int cuda_fail(th_ctx* c, cudaError_t e, const char* what) {
     cudaError_t e__ = (call);                                     \
     if (e__ != cudaSuccess) return cuda_fail((ctx), e__, #call);  \
   } while (0)
+
+inline int gpu_of_id(uint64_t id) { return (int)(id & (kMaxGpus - 1)); }
+inline uint64_t new_id(th_ctx* c, const Gpu& g) { return (c->next_seq.fetch_add(1) << kGpuBits) | (uint64_t)g.index; }
+Gpu* gpu_of(th_ctx* c, uint64_t id) {
+  const int gi = gpu_of_id(id);
+  return gi < (int)c->gpus.size() ? c->gpus[(size_t)gi].get() : nullptr;
+}
+
+cudaError_t get_event(Gpu& g, cudaEvent_t* ev) {
+  if (!g.ev_pool.empty()) { *ev = g.ev_pool.back(); g.ev_pool.pop_back(); return cudaSuccess; }
+  return cudaEventCreateWithFlags(ev, cudaEventDisableTiming);
+}
+void put_event(Gpu& g, cudaEvent_t ev) {
+  if (!ev) return;
+  if (g.ev_pool.size() < 4096) g.ev_pool.push_back(ev);
+  else cudaEventDestroy(ev);
+}
 
 void put_job(Gpu& g, JobBuf* jb) {
   if (!jb->from_arena) { g.free_jobs.push_back(jb); return; }
@@ -173,12 +220,13 @@ void put_job(Gpu& g, JobBuf* jb) {
   g.arena_free[off] = len;
 }
 
-JobBuf* get_job(th_ctx* c, Gpu& g, size_t n, int* rc) {
-  const size_t need = JobBuf::bytes_for(n);
+// `need` bytes of pinned + device staging (same offsets in both).  cap_n records how many messages the block was
+// sized for (0 for odd jobs such as the ETag combine).
+JobBuf* get_buf(th_ctx* c, Gpu& g, size_t need, size_t cap_n, int* rc) {
   for (auto it = g.arena_free.begin(); it != g.arena_free.end(); ++it) {
     if (it->second >= need) {
       JobBuf* jb = new JobBuf();
-      jb->cap_n = n; jb->bytes = need; jb->from_arena = true; jb->arena_off = it->first;
+      jb->cap_n = cap_n; jb->bytes = need; jb->from_arena = true; jb->arena_off = it->first;
       jb->h = g.arena_h + it->first; jb->d = g.arena_d + it->first;
       const size_t rest = it->second - need, off = it->first;
       g.arena_free.erase(it);
@@ -187,25 +235,32 @@ JobBuf* get_job(th_ctx* c, Gpu& g, size_t n, int* rc) {
     }
   }
   for (size_t i = 0; i < g.free_jobs.size(); i++) {
-    if (g.free_jobs[i]->cap_n >= n) {
+    if (g.free_jobs[i]->bytes >= need) {
       JobBuf* jb = g.free_jobs[i];
       g.free_jobs.erase(g.free_jobs.begin() + (long)i);
+      jb->cap_n = cap_n;
       return jb;
     }
   }
+  // Overflow: the arena is full (very many small messages in flight).  These allocations synchronise the device,
+  // which stalls every running chain — callers can see that it happened in th_stats.overflow_allocs.
   JobBuf* jb = new JobBuf();
-  jb->cap_n = std::max<size_t>(n, 1024);
-  jb->bytes = JobBuf::bytes_for(jb->cap_n);
+  jb->cap_n = cap_n;
+  jb->bytes = std::max(need, JobBuf::bytes_for(1024));
   cudaError_t e = cudaHostAlloc((void**)&jb->h, jb->bytes, cudaHostAllocPortable);
   if (e == cudaSuccess) e = cudaMalloc((void**)&jb->d, jb->bytes);
   if (e != cudaSuccess) {
     if (jb->h) cudaFreeHost(jb->h);
     delete jb;
-    *rc = (e == cudaErrorMemoryAllocation) ? TH_ENOMEM : cuda_fail(c, e, "job buffer allocation");
+    if (e == cudaErrorMemoryAllocation) { cudaGetLastError(); *rc = TH_ENOMEM; }
+    else *rc = cuda_fail(c, e, "job buffer allocation");
     return nullptr;
   }
+  g.st.overflow_allocs += 1;
   return jb;
 }
+
+JobBuf* get_job(th_ctx* c, Gpu& g, size_t n, int* rc) { return get_buf(c, g, JobBuf::bytes_for(n), n, rc); }
 
 // order[0..n) = indices 0..n-1 by descending 64-byte block count, stable: LSD radix sort, 3 passes of 11 bits over
 // the complemented count (a comparison sort of 300 k lengths cost 10 ms on the submit path; this is < 2 ms).
@@ -242,6 +297,12 @@ Slot* oldest_host_busy(Gpu& g) {
   return nullptr;
 }
 
+Slot* find_slot(Gpu& g, uint64_t id) {
+  for (auto& s : g.slots)
+    if (s.id == id) return &s;
+  return nullptr;
+}
+
 // Where `need` bytes fit at the tail of a FIFO ring whose live region is [head, tail) modulo one wrap;
 // (size_t)-1 when they do not.
 size_t ring_fit(size_t cap, size_t head, size_t tail, bool idle, size_t need) {
@@ -255,16 +316,24 @@ size_t ring_fit(size_t cap, size_t head, size_t tail, bool idle, size_t need) {
   return (size_t)-1;
 }
 
-cudaError_t ticket_poll(Ticket* t, bool block);
+// cudaEventQuery / cudaEventSynchronize over every tail of a ticket.
+cudaError_t ticket_poll(Ticket* t, bool block) {
+  for (auto& tl : t->tails) {
+    cudaError_t e = block ? cudaEventSynchronize(tl.done) : cudaEventQuery(tl.done);
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
+}
 
 // Marks copied slots' pinned bytes and finished slots' device bytes reusable and advances both ring heads.
+// Called with g.mu held.
 void reap(th_ctx* c, Gpu& g, bool block_on_oldest) {
   for (auto& s : g.slots) {
     if (s.done || !s.submitted) continue;
     bool all = true;
     for (uint64_t id : s.tickets) {
-      auto it = c->tickets.find(id);
-      if (it == c->tickets.end()) continue;  // already retired by th_result
+      auto it = g.tickets.find(id);
+      if (it == g.tickets.end()) continue;  // already retired by th_result
       Ticket* t = it->second;
       if (!t->finished) {
         cudaError_t e = ticket_poll(t, block_on_oldest && &s == &g.slots.front());
@@ -277,7 +346,7 @@ void reap(th_ctx* c, Gpu& g, bool block_on_oldest) {
     if (!s.host_free && s.ev_copied && cudaEventQuery(s.ev_copied) == cudaSuccess) s.host_free = true;
   }
   while (!g.slots.empty() && g.slots.front().done) {
-    if (g.slots.front().ev_copied) cudaEventDestroy(g.slots.front().ev_copied);
+    put_event(g, g.slots.front().ev_copied);
     g.slots.pop_front();
     g.dhead = g.slots.empty() ? g.dtail : g.slots.front().doff;
   }
@@ -287,19 +356,96 @@ void reap(th_ctx* c, Gpu& g, bool block_on_oldest) {
   else g.head = g.tail = 0;
 }
 
-// Runs on CUDA's callback thread once per launch item; the item that finishes last delivers the ticket's callback.
+// Runs on CUDA's callback thread once per launch item.  It may not call CUDA and must not take long: the item that
+// finishes last only hands the ticket's id to the completer thread.
 void CUDART_CB host_item_done(void* p) {
   Ticket* t = static_cast<Ticket*>(p);
-  if (t->cb_left.fetch_sub(1) == 1 && t->cb) t->cb(t->user, t->id, TH_OK);
+  if (t->cb_left.fetch_sub(1) == 1 && t->cb) {
+    th_ctx* c = t->ctx;
+    std::lock_guard<std::mutex> lk(c->cq_mu);
+    c->cq_ready.push_back(t->id);
+    c->cq_cv.notify_one();
+  }
 }
 
-// cudaEventQuery / cudaEventSynchronize over every tail of a ticket.
-cudaError_t ticket_poll(Ticket* t, bool block) {
-  for (auto& tl : t->tails) {
-    cudaError_t e = block ? cudaEventSynchronize(tl.done) : cudaEventQuery(tl.done);
-    if (e != cudaSuccess) return e;
+// Completer thread: delivers the callback of ticket `id` with `status` unless it has been delivered already.
+void deliver(th_ctx* c, uint64_t id, int status) {
+  Gpu* g = gpu_of(c, id);
+  if (!g) return;
+  th_done_cb cb = nullptr;
+  void* user = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g->mu);
+    auto it = g->tickets.find(id);
+    if (it == g->tickets.end() || !it->second->cb || it->second->cb_state != 0) return;
+    Ticket* t = it->second;
+    t->cb_state = 1;
+    if (status != TH_OK) { t->status = status; t->finished = true; }
+    cb = t->cb;
+    user = t->user;
   }
-  return cudaSuccess;
+  cb(user, id, status);  // no lock held: the callback may call th_result / th_wait / th_submit ...
+  {
+    std::lock_guard<std::mutex> lk(g->mu);
+    auto it = g->tickets.find(id);          // gone if the callback retired its own ticket
+    if (it != g->tickets.end()) it->second->cb_state = 2;
+  }
+  c->cb_outstanding.fetch_sub(1);
+  std::lock_guard<std::mutex> lk(c->cq_mu);
+  c->cb_cv.notify_all();
+}
+
+// A faulted device never runs the host functions queued behind the fault, so a caller that only waits for its
+// callback (the N-API shim's Promises) would hang.  Every 100 ms without a completion the completer looks at the
+// events of the tickets that still owe a callback; an event in error state settles all of that GPU's with TH_ECUDA.
+void watchdog(th_ctx* c) {
+  for (auto& gp : c->gpus) {
+    Gpu& g = *gp;
+    std::vector<uint64_t> owed;
+    bool fault = false;
+    {
+      std::lock_guard<std::mutex> lk(g.mu);
+      cudaSetDevice(g.dev);
+      for (auto& kv : g.tickets) {
+        Ticket* t = kv.second;
+        if (!t->cb || t->cb_state != 0) continue;
+        owed.push_back(t->id);
+        if (!fault) {
+          const cudaError_t e = ticket_poll(t, false);
+          if (e != cudaSuccess && e != cudaErrorNotReady) {
+            cuda_fail(c, e, "device fault seen by the completion watchdog");
+            fault = true;
+          }
+        }
+      }
+    }
+    if (fault)
+      for (uint64_t id : owed) deliver(c, id, TH_ECUDA);
+  }
+}
+
+void completer_main(th_ctx* c) {
+  std::unique_lock<std::mutex> lk(c->cq_mu);
+  for (;;) {
+    if (c->cq_ready.empty()) {
+      if (c->stop) return;
+      if (c->cb_outstanding.load() > 0) {
+        if (c->cq_cv.wait_for(lk, std::chrono::milliseconds(100)) == std::cv_status::timeout && c->cq_ready.empty() && !c->stop) {
+          lk.unlock();
+          watchdog(c);
+          lk.lock();
+        }
+      } else {
+        c->cq_cv.wait(lk);
+      }
+      continue;
+    }
+    const uint64_t id = c->cq_ready.front();
+    c->cq_ready.pop_front();
+    lk.unlock();
+    deliver(c, id, TH_OK);
+    lk.lock();
+  }
 }
 
 int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, const th_msg* msgs, size_t n,
@@ -335,21 +481,24 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
   }
   if (expected) std::memcpy(jb->h + jb->o_exp(n), expected, n * 20);
 
+  const bool timing = c->timing.load();
   CU(c, cudaSetDevice(g.dev));
   // H2D: payload (the whole ring slot, once — later submits on the same slot reuse it) then descriptors.
   if (slot && !slot->ev_copied) {
     CU(c, cudaMemcpyAsync(g.ring_d + slot->doff, g.ring_h + slot->off, slot->used, cudaMemcpyHostToDevice, g.s_copy));
     g.st.h2d_bytes += slot->used;
-    CU(c, cudaEventCreateWithFlags(&slot->ev_copied, cudaEventDisableTiming));
+    CU(c, get_event(g, &slot->ev_copied));
     CU(c, cudaEventRecord(slot->ev_copied, g.s_copy));
   }
   const size_t desc_bytes = expected ? jb->o_sha1(n) : (use_order ? jb->o_exp(n) : jb->o_ord(n));
   CU(c, cudaMemcpyAsync(jb->d, jb->h, desc_bytes, cudaMemcpyHostToDevice, g.s_copy));
   g.st.h2d_bytes += desc_bytes;
-  cudaEvent_t ev_in;
-  CU(c, cudaEventCreateWithFlags(&ev_in, c->timing ? cudaEventDefault : cudaEventDisableTiming));
-  CU(c, cudaEventRecord(ev_in, g.s_copy));
+  cudaEvent_t ev_in = nullptr;
+  if (timing) CU(c, cudaEventCreateWithFlags(&ev_in, cudaEventDefault));
+  else CU(c, get_event(g, &ev_in));
   t->ev_ready = ev_in;
+  t->ev_ready_pooled = !timing;
+  CU(c, cudaEventRecord(ev_in, g.s_copy));
 
   const uint64_t* d_off = reinterpret_cast<const uint64_t*>(jb->d + jb->o_off(n)) + m;
   const uint64_t* d_len = reinterpret_cast<const uint64_t*>(jb->d + jb->o_len(n)) + m;
@@ -365,10 +514,10 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
   // which halves its chain latency compared with the per-lane kernel.  Every item after a digest's first runs on
   // another stream of the rotation; each item copies back the digests it produced on its own stream.
   struct Item { size_t first, cnt; int kind; };  // kind 0 prefix, 1 lone, 2 per-lane remainder
-  auto build_items = [&](int a, size_t* skip) {
-    std::vector<Item> items;
-    const bool verify = a == 0 && expected;
-    *skip = 0;
+  struct ItemList { std::vector<Item> items; size_t skip = 0; };
+  auto build_items = [&](bool verify) {
+    ItemList il;
+    std::vector<Item>& items = il.items;
     if (m) items.push_back({0, m, 0});
     if (rest) {
       bool lone_ok = rest <= 64 && !(verify && rest > 1);
@@ -393,17 +542,19 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
         }
         items.push_back({m, rest - peel, 2});
         for (size_t k = 0; k < peel; k++) items.push_back({m + h_ord[m + k], 1, 1});
-        *skip = peel;
+        il.skip = peel;
       }
     }
-    return items;
+    return il;
   };
-  const uint64_t sets = (uint64_t)(c->timing ? std::min(g.n_sets, kTimedStreamSets) : g.n_sets);
+  // the item list depends on the digest only through the fused verify (SHA-1 with an expected table)
+  const bool sha1_verify = (mask & 1u) && expected;
+  const ItemList plain = build_items(false);
+  const ItemList verified = sha1_verify ? build_items(true) : ItemList{};
+  const uint64_t sets = (uint64_t)(timing ? std::min(g.n_sets, kTimedStreamSets) : g.n_sets);
   int n_items = 0;
-  for (int a = 0; a < 3; a++) {
-    size_t skip;
-    if (mask & (1u << a)) n_items += (int)build_items(a, &skip).size();
-  }
+  for (int a = 0; a < 3; a++)
+    if (mask & (1u << a)) n_items += (int)((a == 0 && sha1_verify) ? verified : plain).items.size();
   t->cb_left.store(n_items);
   t->tails.reserve((size_t)n_items);
 
@@ -412,14 +563,15 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
     cudaStream_t st = g.sets[g.next_stream[a]++ % sets].alg[a];
     CU(c, cudaStreamWaitEvent(st, ev_in, 0));
     int rc = TH_OK;
-    if (c->timing) CU(c, cudaEventCreate(&t->ev_k0[a]));
+    if (timing) CU(c, cudaEventCreate(&t->ev_k0[a]));
     uint8_t* d_out = jb->d + out_off[a];
     const uint8_t* d_exp = (a == 0 && expected) ? jb->d + jb->o_exp(n) : nullptr;
     uint32_t* d_ok = (a == 0 && expected) ? reinterpret_cast<uint32_t*>(jb->d + jb->o_ok(n)) : nullptr;
     if (d_ok && use_order) CU(c, cudaMemsetAsync(d_ok + m / 32, 0, ok_bytes - (m / 32) * 4, st));
-    if (c->timing) CU(c, cudaEventRecord(t->ev_k0[a], st));
-    size_t ragged_skip = 0;  // leading entries of the order that are launched alone
-    const std::vector<Item> items = build_items(a, &ragged_skip);
+    if (timing) CU(c, cudaEventRecord(t->ev_k0[a], st));
+    const ItemList& il = (a == 0 && sha1_verify) ? verified : plain;
+    const size_t ragged_skip = il.skip;  // leading entries of the order that are launched alone
+    const std::vector<Item>& items = il.items;
     for (size_t k = 0; k < items.size() && rc == TH_OK; k++) {
       const Item& it = items[k];
       cudaStream_t ps = st;
@@ -446,7 +598,7 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
       if (rc != TH_OK) break;
       g.st.launches += 1;
       Ticket::Tail tl{nullptr, nullptr, a};
-      if (c->timing) {
+      if (timing) {
         CU(c, cudaEventCreate(&tl.k_end));
         CU(c, cudaEventRecord(tl.k_end, ps));
       }
@@ -473,12 +625,12 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
         CU(c, cudaMemcpyAsync(jb->h + jb->o_ok(n) + w0 * 4, jb->d + jb->o_ok(n) + w0 * 4, (w1 - w0) * 4, cudaMemcpyDeviceToHost, ps));
         g.st.d2h_bytes += (w1 - w0) * 4;
       }
-      // the callback is enqueued before `done` so that a ticket cannot be retired (th_result waits on every
-      // `done`) while one of its callbacks is still pending
+      // the host function is enqueued before `done`: once a ticket's `done` events have completed, no host
+      // function of it is still to run, so th_result may free it
       if (t->cb) CU(c, cudaLaunchHostFunc(ps, host_item_done, t));
-      CU(c, cudaEventCreateWithFlags(&tl.done, cudaEventDisableTiming));
+      CU(c, get_event(g, &tl.done));
+      t->tails.push_back(tl);  // (before the record, so that a failing record still leaves the event with its ticket)
       CU(c, cudaEventRecord(tl.done, ps));
-      t->tails.push_back(tl);
     }
     if (rc != TH_OK) {
       if (rc == TH_ECUDA) return cuda_fail(c, cudaGetLastError(), "digest kernel launch");
@@ -503,15 +655,20 @@ int validate(const th_msg* msgs, size_t n, uint32_t mask, size_t limit) {
   return TH_OK;
 }
 
-void free_ticket_events(Ticket* t) {
+void free_ticket_events(Gpu& g, Ticket* t) {
   for (auto& tl : t->tails) {
     if (tl.k_end) cudaEventDestroy(tl.k_end);
-    if (tl.done) cudaEventDestroy(tl.done);
+    put_event(g, tl.done);
   }
   t->tails.clear();
-  if (t->ev_ready) cudaEventDestroy(t->ev_ready);
+  if (t->ev_ready) {
+    if (t->ev_ready_pooled) put_event(g, t->ev_ready);
+    else cudaEventDestroy(t->ev_ready);
+    t->ev_ready = nullptr;
+  }
   for (int a = 0; a < 3; a++) {
     if (t->ev_k0[a]) cudaEventDestroy(t->ev_k0[a]);
+    t->ev_k0[a] = nullptr;
   }
 }
 
@@ -524,7 +681,7 @@ int th_init(const int* gpu_ids, int n_gpus, size_t ring_bytes_per_gpu, th_ctx** 
 }
 
 int th_init_staged(const int* gpu_ids, int n_gpus, size_t ring_bytes_per_gpu, size_t device_bytes_per_gpu, th_ctx** out) {
-  if (!out || n_gpus <= 0) return TH_EINVAL;
+  if (!out || n_gpus <= 0 || n_gpus > kMaxGpus) return TH_EINVAL;
   if (device_bytes_per_gpu == 0) device_bytes_per_gpu = ring_bytes_per_gpu;
   if (ring_bytes_per_gpu == 0) device_bytes_per_gpu = 0;
   *out = nullptr;
@@ -532,9 +689,10 @@ int th_init_staged(const int* gpu_ids, int n_gpus, size_t ring_bytes_per_gpu, si
   int count = 0;
   if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return TH_ENODEVICE;
   th_ctx* c = new th_ctx();
-  c->gpus.resize((size_t)n_gpus);
+  for (int i = 0; i < n_gpus; i++) c->gpus.emplace_back(new Gpu());
   for (int i = 0; i < n_gpus; i++) {
-    Gpu& g = c->gpus[(size_t)i];
+    Gpu& g = *c->gpus[(size_t)i];
+    g.index = i;
     g.dev = gpu_ids ? gpu_ids[i] : i;
     if (const char* e = getenv("TRITONHASH_STREAM_SETS")) {
       const int v = atoi(e);
@@ -542,6 +700,7 @@ int th_init_staged(const int* gpu_ids, int n_gpus, size_t ring_bytes_per_gpu, si
     }
     cudaDeviceProp prop{};
     if (g.dev < 0 || g.dev >= count || cudaGetDeviceProperties(&prop, g.dev) != cudaSuccess || prop.major < 10) {
+      g.dev = -1;
       th_shutdown(c);
       return TH_ENODEVICE;  // kernels are sm_100a only; there is no other path
     }
@@ -566,29 +725,53 @@ int th_init_staged(const int* gpu_ids, int n_gpus, size_t ring_bytes_per_gpu, si
     }
     if (e != cudaSuccess) {
       int rc = (e == cudaErrorMemoryAllocation) ? TH_ENOMEM : TH_ECUDA;
+      cudaGetLastError();
       th_shutdown(c);
       return rc;
     }
   }
-  if (const char* e = getenv("TRITONHASH_TICKET_TIMING")) c->timing = atoi(e) != 0;
+  if (const char* e = getenv("TRITONHASH_TICKET_TIMING")) c->timing.store(atoi(e) != 0);
+  c->completer = std::thread(completer_main, c);
+  c->completer_id = c->completer.get_id();
   *out = c;
   return TH_OK;
 }
 
 int th_set_ticket_timing(th_ctx* c, int on) {
   if (!c) return TH_EINVAL;
-  std::lock_guard<std::mutex> lk(c->mu);
-  c->timing = on != 0;
+  c->timing.store(on != 0);
   return TH_OK;
 }
 
 int th_shutdown(th_ctx* c) {
   if (!c) return TH_EINVAL;
-  for (auto& g : c->gpus) {
+  for (auto& gp : c->gpus) {
+    if (gp->dev < 0) continue;
+    cudaSetDevice(gp->dev);
+    cudaDeviceSynchronize();  // every host function has run: the completer's queue holds all that will ever come
+  }
+  if (c->completer.joinable()) {
+    {
+      std::lock_guard<std::mutex> lk(c->cq_mu);
+      c->stop = true;
+      c->cq_cv.notify_all();
+    }
+    c->completer.join();  // delivers what is queued, then returns
+  }
+  for (auto& gp : c->gpus) {
+    Gpu& g = *gp;
     if (g.dev < 0) continue;
     cudaSetDevice(g.dev);
-    cudaDeviceSynchronize();
+    for (auto& kv : g.tickets) {
+      Ticket* t = kv.second;
+      free_ticket_events(g, t);
+      if (t->jb) { if (!t->jb->from_arena) { cudaFreeHost(t->jb->h); cudaFree(t->jb->d); } delete t->jb; }
+      delete t;
+    }
+    g.tickets.clear();
+    for (auto& s : g.slots) put_event(g, s.ev_copied);
     for (auto* jb : g.free_jobs) { cudaFreeHost(jb->h); cudaFree(jb->d); delete jb; }
+    for (auto ev : g.ev_pool) cudaEventDestroy(ev);
     if (g.arena_h) cudaFreeHost(g.arena_h);
     if (g.arena_d) cudaFree(g.arena_d);
     if (g.ring_h) cudaFreeHost(g.ring_h);
@@ -598,12 +781,6 @@ int th_shutdown(th_ctx* c) {
     if (g.ev_epoch) cudaEventDestroy(g.ev_epoch);
     for (auto& ss : g.sets)
       for (auto& s : ss.alg) if (s) cudaStreamDestroy(s);
-  }
-  for (auto& kv : c->tickets) {
-    Ticket* t = kv.second;
-    free_ticket_events(t);
-    if (t->jb) { if (!t->jb->from_arena) { cudaFreeHost(t->jb->h); cudaFree(t->jb->d); } delete t->jb; }
-    delete t;
   }
   delete c;
   return TH_OK;
@@ -623,9 +800,9 @@ int th_ring_try_acquire(th_ctx* c, int gpu, size_t bytes, void** host_ptr, th_sl
 
 static int ring_acquire(th_ctx* c, int gpu, size_t bytes, void** host_ptr, th_slot* slot, bool wait) {
   if (!c || !host_ptr || !slot || gpu < 0 || gpu >= (int)c->gpus.size() || bytes == 0) return TH_EINVAL;
-  std::lock_guard<std::mutex> lk(c->mu);
-  if (c->sticky) return c->sticky;
-  Gpu& g = c->gpus[(size_t)gpu];
+  if (c->sticky.load()) return c->sticky.load();
+  Gpu& g = *c->gpus[(size_t)gpu];
+  std::lock_guard<std::mutex> lk(g.mu);
   const size_t need = align_up(bytes, kRingAlign);
   if (need > g.ring_bytes || need > g.dring_bytes) return TH_ETOOBIG;
   cudaSetDevice(g.dev);
@@ -636,7 +813,7 @@ static int ring_acquire(th_ctx* c, int gpu, size_t bytes, void** host_ptr, th_sl
     const size_t doff = ring_fit(g.dring_bytes, g.dhead, g.dtail, g.slots.empty(), need);
     if (off != (size_t)-1 && doff != (size_t)-1) {
       Slot s;
-      s.id = c->next_id++;
+      s.id = new_id(c, g);
       s.gpu = gpu;
       s.off = off;
       s.doff = doff;
@@ -661,34 +838,33 @@ static int ring_acquire(th_ctx* c, int gpu, size_t bytes, void** host_ptr, th_sl
     // device ring full: wait for the oldest slot's tickets
     if (!g.slots.front().submitted || !wait) return TH_EBUSY;
     reap(c, g, true);
-    if (c->sticky) return c->sticky;
+    if (c->sticky.load()) return c->sticky.load();
   }
 }
 
 int th_ring_release(th_ctx* c, th_slot slot) {
   if (!c) return TH_EINVAL;
-  std::lock_guard<std::mutex> lk(c->mu);
-  for (auto& g : c->gpus)
-    for (auto& s : g.slots)
-      if (s.id == slot) {
-        if (s.submitted) return TH_ESTATE;
-        s.done = s.host_free = true;
-        reap(c, g, false);
-        return TH_OK;
-      }
-  return TH_ESTATE;
+  Gpu* g = gpu_of(c, slot);
+  if (!g) return TH_ESTATE;
+  std::lock_guard<std::mutex> lk(g->mu);
+  Slot* s = find_slot(*g, slot);
+  if (!s || s->submitted) return TH_ESTATE;
+  s->done = s->host_free = true;
+  cudaSetDevice(g->dev);
+  reap(c, *g, false);
+  return TH_OK;
 }
 
-static int submit_common(th_ctx* c, int gpu, Slot* slot, const void* d_base_user, const th_msg* msgs, size_t n,
+// g.mu held.
+static int submit_common(th_ctx* c, Gpu& g, Slot* slot, const void* d_base_user, const th_msg* msgs, size_t n,
                          uint32_t mask, const uint8_t* expected, th_done_cb cb, void* user, th_ticket* out) {
-  Gpu& g = c->gpus[(size_t)gpu];
   int rc = TH_OK;
   cudaSetDevice(g.dev);
   JobBuf* jb = get_job(c, g, n, &rc);
   if (!jb) return rc;
   Ticket* t = new Ticket();
-  t->id = c->next_id++;
-  t->gpu = gpu;
+  t->id = new_id(c, g);
+  t->gpu = g.index;
   t->n = n;
   t->mask = mask;
   t->has_expected = expected != nullptr && (mask & TH_ALG_SHA1);
@@ -700,16 +876,21 @@ static int submit_common(th_ctx* c, int gpu, Slot* slot, const void* d_base_user
   if (slot) t->slot_id = slot->id;
   rc = enqueue(c, g, t, d_base, slot, msgs, n, mask, t->has_expected ? expected : nullptr);
   if (rc != TH_OK) {
-    // items launched before the failure may still reference the ticket from their host callbacks
-    t->cb = nullptr;
+    // items launched before the failure still reference the ticket from their host functions; they cannot queue
+    // it for delivery (fewer items were enqueued than cb_left counts), but they must have run before it is freed
     cudaDeviceSynchronize();
-    free_ticket_events(t);
+    free_ticket_events(g, t);
     put_job(g, jb);
     delete t;
     return rc;
   }
   if (slot) { slot->submitted = true; slot->tickets.push_back(t->id); }
-  c->tickets[t->id] = t;
+  g.tickets[t->id] = t;
+  if (cb) {
+    c->cb_outstanding.fetch_add(1);
+    std::lock_guard<std::mutex> lk(c->cq_mu);
+    c->cq_cv.notify_one();  // the completer now waits with the watchdog's time-out
+  }
   *out = t->id;
   return TH_OK;
 }
@@ -717,44 +898,68 @@ static int submit_common(th_ctx* c, int gpu, Slot* slot, const void* d_base_user
 int th_submit(th_ctx* c, th_slot slot_id, const th_msg* msgs, size_t n, uint32_t mask, const uint8_t* expected,
               th_done_cb cb, void* user, th_ticket* out) {
   if (!c || !out) return TH_EINVAL;
-  std::lock_guard<std::mutex> lk(c->mu);
-  if (c->sticky) return c->sticky;
-  for (size_t gi = 0; gi < c->gpus.size(); gi++)
-    for (auto& s : c->gpus[gi].slots)
-      if (s.id == slot_id) {
-        if (s.done) return TH_ESTATE;
-        int rc = validate(msgs, n, mask, s.used);
-        if (rc != TH_OK) return rc;
-        return submit_common(c, (int)gi, &s, nullptr, msgs, n, mask, expected, cb, user, out);
-      }
-  return TH_ESTATE;
+  if (c->sticky.load()) return c->sticky.load();
+  Gpu* g = gpu_of(c, slot_id);
+  if (!g) return TH_ESTATE;
+  std::lock_guard<std::mutex> lk(g->mu);
+  Slot* s = find_slot(*g, slot_id);
+  if (!s || s->done) return TH_ESTATE;
+  int rc = validate(msgs, n, mask, s->used);
+  if (rc != TH_OK) return rc;
+  return submit_common(c, *g, s, nullptr, msgs, n, mask, expected, cb, user, out);
 }
 
 int th_submit_device(th_ctx* c, int gpu, const void* d_base, const th_msg* msgs, size_t n, uint32_t mask,
                      const uint8_t* expected, th_done_cb cb, void* user, th_ticket* out) {
   if (!c || !out || gpu < 0 || gpu >= (int)c->gpus.size()) return TH_EINVAL;
   if (reinterpret_cast<uintptr_t>(d_base) & 15) return TH_EALIGN;
-  std::lock_guard<std::mutex> lk(c->mu);
-  if (c->sticky) return c->sticky;
+  if (c->sticky.load()) return c->sticky.load();
   int rc = validate(msgs, n, mask, 0);
   if (rc != TH_OK) return rc;
   if (!d_base) return TH_EINVAL;
-  return submit_common(c, gpu, nullptr, d_base, msgs, n, mask, expected, cb, user, out);
+  Gpu& g = *c->gpus[(size_t)gpu];
+  std::lock_guard<std::mutex> lk(g.mu);
+  return submit_common(c, g, nullptr, d_base, msgs, n, mask, expected, cb, user, out);
 }
 
-static int wait_locked(th_ctx* c, Ticket* t) {
+// Waits for ticket `id` (lk holds g.mu on entry and on return; it is released while blocking, so other threads can
+// keep submitting to this GPU).  Returns the ticket, or nullptr with *rc set.
+static Ticket* wait_ticket(th_ctx* c, Gpu& g, std::unique_lock<std::mutex>& lk, th_ticket id, bool block, int* rc) {
+  auto it = g.tickets.find(id);
+  if (it == g.tickets.end()) { *rc = TH_ESTATE; return nullptr; }
+  Ticket* t = it->second;
   if (!t->finished) {
-    cudaSetDevice(c->gpus[(size_t)t->gpu].dev);
-    cudaError_t e = ticket_poll(t, true);
-    t->finished = true;
-    if (e != cudaSuccess) t->status = cuda_fail(c, e, "cudaEventSynchronize(ticket)");
+    cudaSetDevice(g.dev);
+    if (!block) {
+      const cudaError_t e = ticket_poll(t, false);
+      if (e == cudaErrorNotReady) { *rc = TH_EBUSY; return nullptr; }
+      t->finished = true;
+      if (e != cudaSuccess) t->status = cuda_fail(c, e, "cudaEventQuery(ticket)");
+    } else {
+      std::vector<cudaEvent_t> evs;
+      for (auto& tl : t->tails) evs.push_back(tl.done);
+      lk.unlock();  // the events belong to the ticket, and only its owner (this caller) retires it
+      cudaError_t e = cudaSuccess;
+      for (cudaEvent_t ev : evs) {
+        e = cudaEventSynchronize(ev);
+        if (e != cudaSuccess) break;
+      }
+      lk.lock();
+      it = g.tickets.find(id);
+      if (it == g.tickets.end()) { *rc = TH_ESTATE; return nullptr; }  // retired by another thread meanwhile
+      t = it->second;
+      if (!t->finished) {
+        t->finished = true;
+        if (e != cudaSuccess) t->status = cuda_fail(c, e, "cudaEventSynchronize(ticket)");
+      }
+    }
   }
   if (!t->timed && t->status == TH_OK && t->ev_k0[0] == nullptr && t->ev_k0[1] == nullptr && t->ev_k0[2] == nullptr) {
     t->timed = true;  // submitted with ticket timing off: times stay -1
   }
   if (!t->timed && t->status == TH_OK) {
-    Gpu& g = c->gpus[(size_t)t->gpu];
     float ms = 0.f;
+    cudaSetDevice(g.dev);
     if (t->ev_ready && cudaEventElapsedTime(&ms, g.ev_epoch, t->ev_ready) == cudaSuccess) t->times_ms[0] = ms;
     for (int a = 0; a < 3; a++) {
       if (!t->ev_k0[a]) continue;
@@ -766,34 +971,68 @@ static int wait_locked(th_ctx* c, Ticket* t) {
     }
     t->timed = true;
   }
-  return t->status;
+  *rc = t->status;
+  return t;
 }
 
 int th_ticket_timing(th_ctx* c, th_ticket id, double* ms7) {
   if (!c || !ms7) return TH_EINVAL;
-  std::lock_guard<std::mutex> lk(c->mu);
-  auto it = c->tickets.find(id);
-  if (it == c->tickets.end()) return TH_ESTATE;
-  int rc = wait_locked(c, it->second);
-  for (int i = 0; i < 7; i++) ms7[i] = it->second->times_ms[i];
+  Gpu* g = gpu_of(c, id);
+  if (!g) return TH_ESTATE;
+  std::unique_lock<std::mutex> lk(g->mu);
+  int rc = TH_OK;
+  Ticket* t = wait_ticket(c, *g, lk, id, true, &rc);
+  if (!t) return rc;
+  for (int i = 0; i < 7; i++) ms7[i] = t->times_ms[i];
   return rc;
 }
 
 int th_wait(th_ctx* c, th_ticket id) {
   if (!c) return TH_EINVAL;
-  std::lock_guard<std::mutex> lk(c->mu);
-  auto it = c->tickets.find(id);
-  if (it == c->tickets.end()) return TH_ESTATE;
-  return wait_locked(c, it->second);
+  Gpu* g = gpu_of(c, id);
+  if (!g) return TH_ESTATE;
+  std::unique_lock<std::mutex> lk(g->mu);
+  int rc = TH_OK;
+  wait_ticket(c, *g, lk, id, true, &rc);
+  return rc;
+}
+
+int th_poll(th_ctx* c, th_ticket id) {
+  if (!c) return TH_EINVAL;
+  Gpu* g = gpu_of(c, id);
+  if (!g) return TH_ESTATE;
+  std::unique_lock<std::mutex> lk(g->mu);
+  int rc = TH_OK;
+  wait_ticket(c, *g, lk, id, false, &rc);
+  return rc;
 }
 
 int th_result(th_ctx* c, th_ticket id, uint8_t* sha1, uint8_t* md5, uint8_t* sha256, uint32_t* ok_bits) {
   if (!c) return TH_EINVAL;
-  std::lock_guard<std::mutex> lk(c->mu);
-  auto it = c->tickets.find(id);
-  if (it == c->tickets.end()) return TH_ESTATE;
-  Ticket* t = it->second;
-  int rc = wait_locked(c, t);
+  Gpu* gp = gpu_of(c, id);
+  if (!gp) return TH_ESTATE;
+  Gpu& g = *gp;
+  std::unique_lock<std::mutex> lk(g.mu);
+  int rc = TH_OK;
+  Ticket* t = wait_ticket(c, g, lk, id, true, &rc);
+  if (!t) return rc;
+  // A ticket submitted with a callback is retired only after the callback has returned (its `user` pointer and
+  // the caller's thunk must outlive it) — unless this IS the callback, running on the completer thread.
+  if (t->cb && t->cb_state != 2 && std::this_thread::get_id() != c->completer_id) {
+    for (;;) {
+      lk.unlock();
+      {
+        std::unique_lock<std::mutex> ql(c->cq_mu);
+        c->cb_cv.wait_for(ql, std::chrono::milliseconds(5));
+      }
+      lk.lock();
+      auto it = g.tickets.find(id);
+      if (it == g.tickets.end()) return TH_ESTATE;
+      t = it->second;
+      if (t->cb_state == 2) break;
+    }
+    rc = t->status;
+  }
   const size_t n = t->n;
   JobBuf* jb = t->jb;
   if (rc == TH_OK) {
@@ -802,10 +1041,10 @@ int th_result(th_ctx* c, th_ticket id, uint8_t* sha1, uint8_t* md5, uint8_t* sha
     if (sha256) { if (!(t->mask & TH_ALG_SHA256)) rc = TH_EINVAL; else std::memcpy(sha256, jb->h + jb->o_sha256(n), n * 32); }
     if (ok_bits) { if (!t->has_expected) rc = TH_EINVAL; else std::memcpy(ok_bits, jb->h + jb->o_ok(n), ((n + 31) / 32) * 4); }
   }
-  Gpu& g = c->gpus[(size_t)t->gpu];
-  free_ticket_events(t);
+  cudaSetDevice(g.dev);
+  free_ticket_events(g, t);
   put_job(g, jb);
-  c->tickets.erase(it);
+  g.tickets.erase(id);
   delete t;
   reap(c, g, false);
   return rc;
@@ -815,45 +1054,60 @@ int th_etag_combine(th_ctx* c, int gpu, const uint8_t* md5s, const uint32_t* cou
                     uint8_t* out16) {
   if (!c || gpu < 0 || gpu >= (int)c->gpus.size() || !counts || !out16 || n_objects > 0x7fffffffu) return TH_EINVAL;
   if (n_objects == 0) return TH_OK;
-  std::lock_guard<std::mutex> lk(c->mu);
-  if (c->sticky) return c->sticky;
-  Gpu& g = c->gpus[(size_t)gpu];
-  CU(c, cudaSetDevice(g.dev));
-  std::vector<uint64_t> prefix(n_objects + 1, 0);
-  for (size_t i = 0; i < n_objects; i++) prefix[i + 1] = prefix[i] + counts[i];
-  const size_t parts = (size_t)prefix[n_objects];
+  if (c->sticky.load()) return c->sticky.load();
+  Gpu& g = *c->gpus[(size_t)gpu];
+  size_t parts = 0;
+  for (size_t i = 0; i < n_objects; i++) parts += counts[i];
   if (parts && !md5s) return TH_EINVAL;
-  const size_t b_md5 = align_up(parts * 16 + 16, 256), b_pre = align_up((n_objects + 1) * 8, 256), b_out = n_objects * 16;
-  uint8_t* d = nullptr;
-  CU(c, cudaMalloc((void**)&d, b_md5 + b_pre + b_out));
-  cudaStream_t st = g.s_misc;
-  cudaError_t e = cudaSuccess;
-  if (parts) e = cudaMemcpyAsync(d, md5s, parts * 16, cudaMemcpyHostToDevice, st);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(d + b_md5, prefix.data(), (n_objects + 1) * 8, cudaMemcpyHostToDevice, st);
+  // One block of the staging arena holds the part digests, the prefix sums and the result, pinned and device side:
+  // no allocation (a device-wide synchronisation) happens here, so a combine does not disturb running chains.
+  const size_t b_md5 = align_up(parts * 16 + 16, 256), b_pre = align_up((n_objects + 1) * 8, 256), b_out = align_up(n_objects * 16, 256);
+  JobBuf* jb = nullptr;
+  cudaEvent_t ev = nullptr;
   int rc = TH_OK;
-  if (e == cudaSuccess) rc = th_etag_combine_device(d, reinterpret_cast<uint64_t*>(d + b_md5), (uint32_t)n_objects, d + b_md5 + b_pre, st);
-  if (e == cudaSuccess && rc == TH_OK) e = cudaMemcpyAsync(out16, d + b_md5 + b_pre, b_out, cudaMemcpyDeviceToHost, st);
-  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-  cudaFree(d);
-  if (e != cudaSuccess) return cuda_fail(c, e, "th_etag_combine");
-  if (rc == TH_OK) {
+  {
+    std::lock_guard<std::mutex> lk(g.mu);
+    CU(c, cudaSetDevice(g.dev));
+    jb = get_buf(c, g, b_md5 + b_pre + b_out, 0, &rc);
+    if (!jb) return rc;
+    if (parts) std::memcpy(jb->h, md5s, parts * 16);
+    uint64_t* prefix = reinterpret_cast<uint64_t*>(jb->h + b_md5);
+    prefix[0] = 0;
+    for (size_t i = 0; i < n_objects; i++) prefix[i + 1] = prefix[i] + counts[i];
+    cudaStream_t st = g.s_misc;
+    cudaError_t e = cudaMemcpyAsync(jb->d, jb->h, b_md5 + b_pre, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) rc = th_etag_combine_device(jb->d, reinterpret_cast<uint64_t*>(jb->d + b_md5), (uint32_t)n_objects, jb->d + b_md5 + b_pre, st);
+    if (e == cudaSuccess && rc == TH_OK) e = cudaMemcpyAsync(jb->h + b_md5 + b_pre, jb->d + b_md5 + b_pre, n_objects * 16, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = get_event(g, &ev);
+    if (e == cudaSuccess) e = cudaEventRecord(ev, st);
+    if (e != cudaSuccess || rc != TH_OK) {
+      cudaStreamSynchronize(st);
+      put_event(g, ev);
+      put_job(g, jb);
+      return e != cudaSuccess ? cuda_fail(c, e, "th_etag_combine") : rc;
+    }
     g.st.launches += 1;
-    g.st.h2d_bytes += parts * 16 + (n_objects + 1) * 8;
-    g.st.d2h_bytes += b_out;
+    g.st.h2d_bytes += b_md5 + b_pre;
+    g.st.d2h_bytes += n_objects * 16;
   }
-  return rc;
+  const cudaError_t e = cudaEventSynchronize(ev);  // outside the lock: submits to this GPU go on meanwhile
+  std::lock_guard<std::mutex> lk(g.mu);
+  if (e == cudaSuccess) std::memcpy(out16, jb->h + b_md5 + b_pre, n_objects * 16);
+  put_event(g, ev);
+  put_job(g, jb);
+  return e == cudaSuccess ? TH_OK : cuda_fail(c, e, "th_etag_combine");
 }
 
 int th_stats_get(th_ctx* c, int gpu, th_stats* out) {
   if (!c || !out || gpu >= (int)c->gpus.size()) return TH_EINVAL;
-  std::lock_guard<std::mutex> lk(c->mu);
   std::memset(out, 0, sizeof(*out));
   for (size_t i = 0; i < c->gpus.size(); i++) {
     if (gpu >= 0 && (int)i != gpu) continue;
-    const th_stats& s = c->gpus[i].st;
+    std::lock_guard<std::mutex> lk(c->gpus[i]->mu);
+    const th_stats& s = c->gpus[i]->st;
     out->messages += s.messages; out->bytes += s.bytes; out->launches += s.launches;
     out->h2d_bytes += s.h2d_bytes; out->d2h_bytes += s.d2h_bytes; out->submits += s.submits;
-    out->kernel_ms += s.kernel_ms;
+    out->kernel_ms += s.kernel_ms; out->overflow_allocs += s.overflow_allocs;
   }
   return TH_OK;
 }
@@ -866,14 +1120,14 @@ const char* th_strerror(int code) {
     case TH_ECUDA: return "CUDA runtime error (see th_last_error)";
     case TH_ENOMEM: return "out of host or device memory";
     case TH_EALIGN: return "message offset or base pointer is not 16-byte aligned";
-    case TH_EBUSY: return "ring full and its oldest slot has not been submitted";
+    case TH_EBUSY: return "not ready: ring full and its oldest slot has not been submitted, or ticket still running (th_poll)";
     case TH_ETOOBIG: return "request exceeds the ring size or a fixed limit";
     case TH_ESTATE: return "unknown ticket/slot or call out of order";
     default: return "unknown error";
   }
 }
 
-const char* th_last_error(const th_ctx* c) { return c ? c->last_error.c_str() : ""; }
+const char* th_last_error(const th_ctx* c) { return c ? c->last_error : ""; }
 
 void th_hex(const uint8_t* in, size_t n, char* out) {
   static const char d[] = "0123456789abcdef";

@@ -85,6 +85,9 @@ class Engine:
         return arr
 
     def submit(self, slot: int, offsets, lengths, algs: int, expected_sha1=None, callback=None) -> int:
+        """th_submit.  callback(ticket, status), if given, is delivered once on the library's completion thread
+        with the ticket's real status (TH_OK = 0, or -3 when the device faulted); it may call result() / wait() /
+        submit() of this engine, and the ticket must still be retired with result() whatever the status."""
         msgs = self._msgs(offsets, lengths)
         exp = None
         if expected_sha1 is not None:
@@ -126,6 +129,14 @@ class Engine:
 
     def wait(self, ticket: int) -> None:
         check(self._L.th_wait(self._ctx, ticket), "th_wait", self._ctx)
+
+    def poll(self, ticket: int) -> bool:
+        """th_poll: True when the ticket's digests are in host memory, False while it runs; never blocks."""
+        rc = self._L.th_poll(self._ctx, ticket)
+        if rc == -6:  # TH_EBUSY
+            return False
+        check(rc, "th_poll", self._ctx)
+        return True
 
     def result(self, ticket: int, n: int, algs: int, want_ok: bool = False) -> dict:
         out = {}

@@ -12,8 +12,15 @@
  *   - there is NO CPU fallback: without a usable GPU th_init fails with TH_ENODEVICE.
  *   - digests are raw bytes in the standard byte order (what crypto's .digest() Buffer holds):
  *     SHA-1 20 B, MD5 16 B, SHA-256 32 B.  hex / base64 are th_hex / th_base64.
- *   - message start addresses must be 16-byte aligned on the device (TH_EALIGN otherwise): the
- *     kernels stage each lane's message with 1-D bulk async copies (cp.async.bulk).
+ *   - message start addresses must be 16-byte aligned on the device: equal-length batches are staged
+ *     by 2-D TMA tiles (a tensor map over {n rows x len bytes}, 16-byte row pitch) and ragged batches by
+ *     16-byte cp.async copies.  Everything the HOST can see is checked and refused with TH_EALIGN — the
+ *     base pointer, the stride, and every th_msg.offset of th_submit / th_submit_device.  Offsets that
+ *     exist only in DEVICE memory (d_offsets of the launch-level calls and of th_digest_ragged_static)
+ *     cannot be inspected without a synchronising copy and are NOT validated: a misaligned one faults
+ *     in the kernel (a sticky CUDA error), it does not come back as TH_EALIGN.
+ *   - thread safety: every th_* call on a context may be made from any thread.  Each GPU of a context
+ *     has its own lock, so threads feeding different GPUs do not wait for each other.
  */
 #ifndef TRITONHASH_H
 #define TRITONHASH_H
@@ -62,10 +69,22 @@ typedef struct th_stats {
   uint64_t d2h_bytes;   /* bytes copied device -> host (digests, ok words) */
   uint64_t submits;
   double kernel_ms;     /* summed device time of digest kernels (CUDA events; only while ticket timing is on) */
+  uint64_t overflow_allocs; /* job buffers that did not fit the staging arena and were allocated on the submit
+                               path (cudaHostAlloc + cudaMalloc synchronise the device: every running chain
+                               stalls).  Non-zero = size the rings larger, or submit fewer tiny messages at once */
 } th_stats;
 
-/* Completion callback, delivered on a library (CUDA host-callback) thread — the N-API shim
- * forwards it with a napi_threadsafe_function.  status is TH_OK or TH_ECUDA. */
+/* Completion callback.  Delivered once per ticket on the context's completion thread (a library thread, not
+ * CUDA's own callback thread) with no library lock held — the N-API shim forwards it to the JS thread with a
+ * napi_threadsafe_function.
+ *   - status is the ticket's real outcome: TH_OK, or TH_ECUDA when the device faulted.  A faulted device never
+ *     signals completion by itself, so the completion thread doubles as a watchdog: within about 100 ms of a
+ *     fault every ticket that still owes a callback gets it with TH_ECUDA (the reference would throw and nack).
+ *   - the callback MAY call th_result / th_wait / th_poll / th_submit / th_ring_* on the same context, and may
+ *     retire its own ticket; it must not call th_shutdown, and while it runs no other callback is delivered.
+ *   - the ticket must still be retired with th_result whatever the status (it frees the ticket's buffers);
+ *     th_result called from another thread waits until the callback has returned, so `user` may be freed
+ *     right after th_result. */
 typedef void (*th_done_cb)(void* user, th_ticket ticket, int status);
 
 /* ---- context ------------------------------------------------------------------------------
@@ -129,6 +148,11 @@ int th_set_ticket_timing(th_ctx* ctx, int on);
 
 /* Blocks until the ticket's digests are in host memory. */
 int th_wait(th_ctx* ctx, th_ticket ticket);
+/* Never blocks: TH_OK when the ticket's digests are in host memory, TH_EBUSY while it is still running, the
+ * ticket's error otherwise.  For callers that may not block and do not use callbacks (a poll from Node's event
+ * loop, or one thread collecting from several GPUs in whatever order they finish).  No counterpart in the
+ * reference (Node's crypto is synchronous). */
+int th_poll(th_ctx* ctx, th_ticket ticket);
 /* Copies results out (any pointer may be NULL) and retires the ticket.  Waits if needed.
  * sha1: n*20, md5: n*16, sha256: n*32, ok_bits: ceil(n/32) words, bit (i&31) of word i>>5. */
 int th_result(th_ctx* ctx, th_ticket ticket, uint8_t* sha1, uint8_t* md5, uint8_t* sha256,
@@ -137,6 +161,8 @@ int th_result(th_ctx* ctx, th_ticket ticket, uint8_t* sha1, uint8_t* md5, uint8_
 /* Multipart object ETag: out16[j] = md5(md5s of object j's parts, concatenated), computed on the
  * GPU by one warp per object (message words travel by warp shuffle).  counts[j] = parts of object j,
  * md5s = all part digests back to back (host memory).  The S3 ETag string is hex(out16)+"-"+count.
+ * Blocks until the result is in out16 but allocates nothing (its buffers come from the context's staging
+ * arena), so calling it per object does not stall digest chains that are running on the GPU.
  * Replaces the ETag the S3 server returns to [dep] minio completeMultipartUpload (lib/upload.js:45). */
 int th_etag_combine(th_ctx* ctx, int gpu, const uint8_t* md5s, const uint32_t* counts,
                     size_t n_objects, uint8_t* out16);
@@ -191,6 +217,14 @@ int th_synth_fill(void* d_dst, uint64_t first_msg, uint64_t n, uint64_t len, uin
  *     verification) are device pointers as in the launch-level calls; d_ok_bits is cleared here;
  *   - the first call on each device looks up the table's device address (cudaGetSymbolAddress) with
  *     that device current; make that first call before you start capturing the stream;
+ *   - "calls no allocator" is about this function's own code.  The CUDA driver itself places a library's
+ *     kernels and __device__ arrays in device memory when the library is first used on a device, and
+ *     that can be this call.  So make the first call on each device (n = 1 is enough), or any other launch
+ *     from this library, BEFORE your application hands the last of HBM to its own pools; if the driver
+ *     cannot place the library image any more the call returns TH_ENOMEM;
+ *   - arguments the host can check (alg, NULL pointers, n, the alignment of d_base) are refused before
+ *     anything is enqueued on the stream; d_offsets lives in device memory and is not inspected: every
+ *     offset must be a multiple of 16 or the kernel faults (see the conventions at the top);
  *   - all calls on a device share the one table, which keeps what the last call left in it: the
  *     counters are cleared at the start of each call, and two calls whose work overlaps on the GPU
  *     (different streams) race on it — serialise them. */

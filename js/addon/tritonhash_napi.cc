@@ -1,8 +1,9 @@
 // tritonhash_napi.cc — N-API binding of include/tritonhash.h.  The image has no node_api.h and no Node.js
 // (js/README.md): a CPU test type-checks it against N-API's documented prototypes (tests/stubs/node_api.h) and links
 // it against libtritonhash.so, and a GPU test executes it under a miniature N-API runtime (tests/napi_mock/).  One th_ctx per process; every call that touches the GPU is
-// asynchronous: th_submit enqueues, the library's completion callback (a CUDA host-callback thread) hops to
-// the JS thread through a napi_threadsafe_function, and th_result fills the Buffers the Promise resolves with.
+// asynchronous: th_submit enqueues, the library's completion callback (delivered on the context's completion
+// thread, also when the device has faulted — then with TH_ECUDA) hops to the JS thread through a
+// napi_threadsafe_function, and th_result fills the Buffers the Promise resolves with (or the Promise rejects).
 #include <node_api.h>
 
 #include <cstring>
@@ -40,7 +41,7 @@ struct Job {
   bool verify = false;
 };
 
-// CUDA host-callback thread: no napi_env here, only the thread-safe hop.
+// Library completion thread: no napi_env here, only the thread-safe hop.
 void on_done(void* user, th_ticket, int status) {
   Job* j = static_cast<Job*>(user);
   napi_call_threadsafe_function(j->tsfn, reinterpret_cast<void*>(static_cast<intptr_t>(status)), napi_tsfn_nonblocking);
@@ -63,14 +64,16 @@ void finish(napi_env env, napi_value, void* context, void* data) {
   if (j->algs & TH_ALG_MD5) { v = make_buffer(env, j->n * 16, &p5); napi_set_named_property(env, result, "md5", v); }
   if (j->algs & TH_ALG_SHA256) { v = make_buffer(env, j->n * 32, &p256); napi_set_named_property(env, result, "sha256", v); }
   if (j->verify) { v = make_buffer(env, ((j->n + 31) / 32) * 4, &pok); napi_set_named_property(env, result, "okBits", v); }
-  if (status == TH_OK)
-    status = th_result(g_ctx, j->ticket, static_cast<uint8_t*>(p1), static_cast<uint8_t*>(p5),
-                       static_cast<uint8_t*>(p256), static_cast<uint32_t*>(pok));
+  // th_result is called whatever the status: it is what retires the ticket and gives its buffers back
+  const int rc = th_result(g_ctx, j->ticket, static_cast<uint8_t*>(p1), static_cast<uint8_t*>(p5),
+                           static_cast<uint8_t*>(p256), static_cast<uint32_t*>(pok));
+  if (status == TH_OK) status = rc;
   if (status == TH_OK) {
     napi_resolve_deferred(env, j->deferred, result);
   } else {
     napi_value msg, err;
     std::string text = std::string("hashBatch: ") + th_strerror(status);
+    if (status == TH_ECUDA && g_ctx) text += std::string(" — ") + th_last_error(g_ctx);
     napi_create_string_utf8(env, text.c_str(), NAPI_AUTO_LENGTH, &msg);
     napi_create_error(env, nullptr, msg, &err);
     napi_reject_deferred(env, j->deferred, err);  // the stage throws -> lib/main.js nacks, as today
@@ -239,7 +242,7 @@ napi_value Stats(napi_env env, napi_callback_info) {
   napi_create_object(env, &o);
   const struct { const char* k; double val; } f[] = {{"messages", (double)s.messages}, {"bytes", (double)s.bytes},
       {"launches", (double)s.launches}, {"h2dBytes", (double)s.h2d_bytes}, {"d2hBytes", (double)s.d2h_bytes},
-      {"submits", (double)s.submits}, {"kernelMs", s.kernel_ms}};
+      {"submits", (double)s.submits}, {"kernelMs", s.kernel_ms}, {"overflowAllocs", (double)s.overflow_allocs}};
   for (const auto& e : f) { napi_create_double(env, e.val, &v); napi_set_named_property(env, o, e.k, v); }
   return o;
 }
