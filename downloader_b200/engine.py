@@ -174,10 +174,14 @@ class Engine:
             offsets[i] = pos
             pos = _align16(pos + b.size)
         slot, view = self.ring_acquire(max(pos, 16), gpu)
-        for i, b in enumerate(bufs):
-            o = int(offsets[i])
-            view[o:o + b.size] = b
-        t = self.submit(slot, offsets, lengths, algs, expected_sha1)
+        try:
+            for i, b in enumerate(bufs):
+                o = int(offsets[i])
+                view[o:o + b.size] = b
+            t = self.submit(slot, offsets, lengths, algs, expected_sha1)
+        except BaseException:
+            self.ring_release(slot)  # a slot that is neither submitted nor released blocks the FIFO ring for good
+            raise
         return self.result(t, n, algs, want_ok=expected_sha1 is not None and bool(algs & ALG_SHA1))
 
     def etag_combine(self, md5s, counts: Sequence[int], gpu: int = 0) -> np.ndarray:

@@ -143,17 +143,18 @@ def _stream_messages(engine, src: _ConcatFiles, bounds: Sequence[Tuple[int, int]
         drain(in_flight - 1)
         slot, view = engine.ring_acquire(max(pos, 16), gpu)
         contiguous = all(bounds[k + 1][0] == bounds[k][1] and (bounds[k][1] - bounds[k][0]) % 16 == 0 for k in range(i, j - 1))
-        try:
+        try:  # an acquired slot that is neither submitted nor released would block the FIFO ring for good
             if contiguous:  # pieces / parts back to back: one sequential read for the whole slot
                 src.readinto(view[:bounds[j - 1][1] - bounds[i][0]], bounds[i][0])
             else:
                 for k in range(i, j):
                     src.readinto(view[offs[k - i]:offs[k - i] + lens[k - i]], bounds[k][0])
+            exp = expected_sha1[i:j] if expected_sha1 is not None else None
+            ticket = engine.submit(slot, np.array(offs, np.uint64), np.array(lens, np.uint64), algs, exp)
         except BaseException:
-            engine.ring_release(slot)  # an unsubmitted slot would block the ring for good
+            engine.ring_release(slot)
             raise
-        exp = expected_sha1[i:j] if expected_sha1 is not None else None
-        pending.append((engine.submit(slot, np.array(offs, np.uint64), np.array(lens, np.uint64), algs, exp), i, j - i))
+        pending.append((ticket, i, j - i))
         i = j
     drain(0)
     if ok is not None:
@@ -178,16 +179,33 @@ def piece_bounds(total: int, piece_length: int) -> List[Tuple[int, int]]:
 
 
 def verify_pieces(engine, files: Sequence[Tuple[str, int]], piece_length: int, expected_sha1, gpu: int = 0,
-                  batch_bytes: int = 256 << 20, in_flight: Optional[int] = None) -> dict:
+                  batch_bytes: int = 256 << 20, in_flight: Optional[int] = None, indices: Optional[Sequence[int]] = None) -> dict:
     """Bulk re-verify of an on-disk download ([dep] webtorrent `_verifyPieces`): returns {'ok': bool[n]
-    (the bitfield), ALG_SHA1: digests}.  Missing files hash as zeros and simply fail verification."""
+    (the bitfield), ALG_SHA1: digests}.  Missing files hash as zeros and simply fail verification.
+
+    indices: verify only these pieces (ascending) — webtorrent's per-piece `onChunk` shape (call site
+    lib/download.js:64-66): after a refetch only the pieces that were requested again are read, copied and hashed,
+    not the whole download.  expected_sha1 stays the full info.pieces table; 'ok' and the digests then have one row
+    per requested index, in that order ('indices' echoes them)."""
     src = _ConcatFiles(files)
     bounds = piece_bounds(src.total, piece_length)
     exp = np.ascontiguousarray(expected_sha1, np.uint8).reshape(-1, 20)
     if exp.shape[0] != len(bounds):
         raise ValueError(f"expected {len(bounds)} piece digests, got {exp.shape[0]}")
+    idx = None
+    if indices is not None:
+        idx = np.asarray(list(indices), np.int64)
+        if idx.size and (idx.min() < 0 or idx.max() >= len(bounds) or (np.diff(idx) <= 0).any()):
+            raise ValueError("piece indices must be ascending, unique and within the torrent")
+        bounds = [bounds[int(i)] for i in idx]
+        exp = exp[idx]
     try:
-        return _stream_messages(engine, src, bounds, ALG_SHA1, exp, gpu, batch_bytes, in_flight)
+        if not bounds:
+            return {ALG_SHA1: np.zeros((0, 20), np.uint8), "ok": np.zeros(0, bool), "indices": idx}
+        out = _stream_messages(engine, src, bounds, ALG_SHA1, exp, gpu, batch_bytes, in_flight)
+        if idx is not None:
+            out["indices"] = idx
+        return out
     finally:
         src.close()
 
@@ -206,6 +224,9 @@ def hash_media_file(engine, path: str, piece_length: int, expected_sha1, part_ra
     if exp is not None:
         pieces["ok"] = np.zeros(len(pb), bool)
     parts = {a: np.zeros((len(part_ranges), DIGEST_LEN[a]), np.uint8) for a in (ALG_MD5, ALG_SHA256) if part_algs & a}
+    for s0, e0 in part_ranges:  # checked before any slot is taken: a slot holds whole pieces and whole parts
+        if s0 % piece_length or (e0 % piece_length and e0 != size):
+            raise ValueError("part boundaries must be multiples of the piece length")
     src = _ConcatFiles([(path, size)])
     pending: List[tuple] = []
     in_flight = _slots_in_flight(engine, batch_bytes, in_flight)
@@ -230,22 +251,24 @@ def hash_media_file(engine, path: str, piece_length: int, expected_sha1, part_ra
                 q1 += 1
             q1 = max(q1, q + 1)
             end = part_ranges[q1 - 1][1]
-            if start % piece_length:
-                raise ValueError("part boundaries must be multiples of the piece length")
             drain(in_flight - 1)
             slot, view = engine.ring_acquire(max(end - start, 16), gpu)
+            tp = None
             try:
                 src.readinto(view[:end - start], start)
+                p0, p1 = start // piece_length, -(-end // piece_length)
+                offs = np.array([pb[i][0] - start for i in range(p0, p1)], np.uint64)
+                lens = np.array([pb[i][1] - pb[i][0] for i in range(p0, p1)], np.uint64)
+                tp = engine.submit(slot, offs, lens, ALG_SHA1, exp[p0:p1] if exp is not None else None)
+                offs = np.array([part_ranges[i][0] - start for i in range(q, q1)], np.uint64)
+                lens = np.array([part_ranges[i][1] - part_ranges[i][0] for i in range(q, q1)], np.uint64)
+                tq = engine.submit(slot, offs, lens, part_algs)   # same slot, second message list: no second copy
             except BaseException:
-                engine.ring_release(slot)  # an unsubmitted slot would block the ring for good
+                if tp is None:
+                    engine.ring_release(slot)  # an unsubmitted slot would block the ring for good
+                else:
+                    engine.result(tp, p1 - p0, ALG_SHA1)  # submitted once: retire that ticket, the slot then frees itself
                 raise
-            p0, p1 = start // piece_length, -(-end // piece_length)
-            offs = np.array([pb[i][0] - start for i in range(p0, p1)], np.uint64)
-            lens = np.array([pb[i][1] - pb[i][0] for i in range(p0, p1)], np.uint64)
-            tp = engine.submit(slot, offs, lens, ALG_SHA1, exp[p0:p1] if exp is not None else None)
-            offs = np.array([part_ranges[i][0] - start for i in range(q, q1)], np.uint64)
-            lens = np.array([part_ranges[i][1] - part_ranges[i][0] for i in range(q, q1)], np.uint64)
-            tq = engine.submit(slot, offs, lens, part_algs)   # same slot, second message list: no second copy
             pending.append((tp, p0, p1 - p0, tq, q, q1 - q))
             q = q1
         drain(0)

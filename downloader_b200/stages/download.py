@@ -16,6 +16,8 @@ import os
 import shutil
 import urllib.parse
 
+import numpy as np
+
 from .. import torrent as tor
 from ..reader import verify_pieces
 from . import SourceType, TelemetryStatus
@@ -39,21 +41,25 @@ async def factory(config, emitter, logger):
         logger.debug("hash", meta.info_hash)
         logger.debug("files", len(meta.files))
         files = meta.on_disk(download_path)
-        bitfield = None
+        # Round 0 is webtorrent's bulk `_verifyPieces` of whatever is on disk.  After a refetch only the pieces that
+        # were requested again are read, copied over PCIe and hashed (the per-piece `onChunk` shape,
+        # lib/download.js:64-66): O(missing bytes) per round, not O(torrent).
+        res = verify_pieces(engine, files, meta.piece_length, meta.pieces)
+        bitfield = res["ok"].copy()
         for _ in range(MAX_REFETCH_ROUNDS + 1):
-            res = verify_pieces(engine, files, meta.piece_length, meta.pieces)  # webtorrent _verifyPieces
-            progressed = bitfield is None or int(res["ok"].sum()) > int(bitfield.sum())
-            bitfield = res["ok"]
             await tel.emitProgress(file_id, TelemetryStatus.DOWNLOADING, int(bitfield.mean() * 100) // 2)
             if bitfield.all():
                 return {"infoHash": meta.info_hash, "bitfield": bitfield}
-            if fetcher is None or not progressed:
-                err = DownloadStalled("Download stalled.")
-                raise err
+            if fetcher is None:
+                raise DownloadStalled("Download stalled.")
             missing = [int(i) for i in (~bitfield).nonzero()[0]]
             for i in missing:
                 logger.warn(f"Piece {i} failed verification")
             await fetcher(meta, missing, download_path)
+            res = verify_pieces(engine, files, meta.piece_length, meta.pieces, indices=missing)
+            if not res["ok"].any():  # a round that repaired nothing: the swarm cannot supply these pieces
+                raise DownloadStalled("Download stalled.")
+            bitfield[np.asarray(missing)[res["ok"]]] = True
         raise DownloadStalled("Download stalled.")
 
     async def http(resource_url, file_id, download_path, job):

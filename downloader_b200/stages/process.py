@@ -3,14 +3,28 @@ test/process/filter_dirs.js:17-82).  Pure directory walk, no hashing; kept so th
 download -> process -> upload hands the same objects around (`{path}` -> `{files, downloadPath}`)."""
 from __future__ import annotations
 
+import json
 import os
 import re
 
 from . import MediaType
 
-MEDIA_EXTS = (".mp4", ".mkv", ".mov", ".webm")          # lib/process.js:15-20
-_RE_SKIP = re.compile(r"/extras|/commentary", re.I)      # lib/process.js:59
-_RE_SEASON = re.compile(r"s\d+|season", re.I)            # lib/process.js:64
+# One rule table for this mirror and for js/lib/process.js (which cannot be executed here): both read
+# js/lib/process_rules.json, so the copy that is tested and the copy that ships cannot drift apart.
+_RULES_PATH = os.path.join(os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))), "js", "lib", "process_rules.json")
+with open(_RULES_PATH) as _f:
+    RULES = json.load(_f)
+
+
+def _js_regex(rule) -> "re.Pattern":
+    """The JSON holds JavaScript regex sources; the ones used here (alternation, \\d, an escaped '/') mean the same in Python."""
+    flags = re.I if "i" in rule.get("flags", "") else 0
+    return re.compile(rule["source"].replace("\\/", "/"), flags)
+
+
+MEDIA_EXTS = tuple(RULES["mediaExts"])                   # lib/process.js:15-20
+_RE_SKIP = _js_regex(RULES["skipDirectory"])              # lib/process.js:59
+_RE_SEASON = _js_regex(RULES["seasonDirectory"])          # lib/process.js:64
 
 
 async def find_media_files(abs_path: str, media, logger) -> list:
@@ -60,7 +74,7 @@ async def factory(config, emitter, logger):
         logger.info("processing directory", file["path"])
         found = await find_media_files(file["path"], job["media"], logger)
         if len(found) == 0:
-            raise RuntimeError("Failed to find any suitable media files")
+            raise RuntimeError(RULES["noMediaError"])
         logger.info("found", len(found), "media files")
         return {"files": found, "downloadPath": file["path"]}
     return stage

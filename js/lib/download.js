@@ -19,38 +19,56 @@ const th = require('./tritonhash')
 const STALL_MS = 240000
 const IN_FLIGHT = 4 // slots submitted and not yet collected
 
-/** Re-hash a download directory against info.pieces; returns the verified bitfield as boolean[] */
-async function verifyOnDisk (files, pieceLength, pieces /* Buffer n*20 */, gpu = 0, slotBytes = 256 * 1024 * 1024) {
+/**
+ * Hash pieces of a download directory against info.pieces; returns the verified bitfield as boolean[nPieces].
+ * `only` (ascending piece indices) restricts the pass to those pieces — after a refetch only what was requested
+ * again is read, copied and hashed (webtorrent verifies a piece when it completes, lib/download.js:64-66);
+ * entries of the result for pieces that were not asked about are `undefined`.
+ */
+async function verifyOnDisk (files, pieceLength, pieces /* Buffer n*20 */, gpu = 0, slotBytes = 256 * 1024 * 1024, only = null) {
   const total = files.reduce((s, f) => s + f.length, 0)
   const nPieces = Math.ceil(total / pieceLength)
-  const ok = new Array(nPieces).fill(false)
+  const todo = only || Array.from({ length: nPieces }, (_, i) => i)
+  const ok = new Array(nPieces).fill(only ? undefined : false)
   const perSlot = Math.max(1, Math.floor(slotBytes / pieceLength))
   const handles = await Promise.all(files.map(f => fsp.open(f.path, 'r').catch(() => null)))
+  const starts = []
+  files.reduce((pos, f) => { starts.push(pos); return pos + f.length }, 0)
   const pending = []
-  const collect = ({ r, first, count }) => { for (let k = 0; k < count; k++) ok[first + k] = r.ok[k] }
+  const collect = ({ r, batch }) => { for (let k = 0; k < batch.length; k++) ok[batch[k]] = r.ok[k] }
+  // stream bytes [lo, hi) of the files laid end to end (as the torrent sees them) -> buffer at `at`; gaps read as zeros
+  const readRange = async (buffer, at, lo, hi) => {
+    for (let i = 0; i < files.length; i++) {
+      const a = Math.max(lo, starts[i])
+      const b = Math.min(hi, starts[i] + files[i].length)
+      if (b <= a) continue
+      if (handles[i]) await th.readFully(handles[i], buffer, at + (a - lo), b - a, a - starts[i], 'zero')
+      else buffer.fill(0, at + (a - lo), at + (b - lo))
+    }
+  }
   try {
-    for (let first = 0; first < nPieces; first += perSlot) {
-      const count = Math.min(perSlot, nPieces - first)
-      const start = first * pieceLength
-      const bytes = Math.min(count * pieceLength, total - start)
+    for (let t = 0; t < todo.length; t += perSlot) {
+      const batch = todo.slice(t, t + perSlot)
+      const lens = batch.map(i => Math.min(pieceLength, total - i * pieceLength))
+      const bytes = (batch.length - 1) * pieceLength + lens[lens.length - 1]
       const { slot, buffer } = await th.ringAcquire(gpu, bytes, pending, collect)
-      buffer.fill(0, 0, bytes)
-      let pos = 0
+      let submitted
       try {
-        for (let i = 0; i < files.length; i++) { // files laid end to end, as the torrent sees them
-          const lo = Math.max(start, pos)
-          const hi = Math.min(start + bytes, pos + files[i].length)
-          if (hi > lo && handles[i]) await handles[i].read(buffer, lo - start, hi - lo, lo - pos)
-          pos += files[i].length
+        for (let k = 0; k < batch.length;) { // consecutive pieces are one read
+          let e = k + 1
+          while (e < batch.length && batch[e] === batch[e - 1] + 1) e++
+          await readRange(buffer, k * pieceLength, batch[k] * pieceLength, batch[e - 1] * pieceLength + lens[e - 1])
+          k = e
         }
+        const msgs = batch.map((_, k) => ({ offset: k * pieceLength, length: lens[k] }))
+        const expected = Buffer.concat(batch.map(i => pieces.slice(i * 20, i * 20 + 20)))
+        submitted = th.sha1Batch(slot, msgs, expected)
       } catch (err) {
-        th.ringRelease(slot) // an unsubmitted slot would block the ring for good
+        th.ringRelease(slot) // a slot that is neither submitted nor released would block the ring for good
         throw err
       }
-      const msgs = []
-      for (let k = 0; k < count; k++) msgs.push({ offset: k * pieceLength, length: Math.min(pieceLength, total - (first + k) * pieceLength) })
       // keep reading while the slot is hashed: digests are collected a few slots later
-      pending.push(th.sha1Batch(slot, msgs, pieces.slice(first * 20, (first + count) * 20)).then(r => ({ r, first, count })))
+      pending.push(submitted.then(r => ({ r, batch })))
       if (pending.length >= IN_FLIGHT) collect(await pending.shift())
     }
     while (pending.length) collect(await pending.shift())
@@ -69,21 +87,25 @@ module.exports = async (config, emitter, logger) => {
     torrent: async (uri, id, downloadPath) => {
       const client = config.torrentClient
       const torrent = await client.fetch(uri, { path: downloadPath }) // metadata + transport, verification off
-      let last = -1
+      const files = torrent.files.map(f => ({ path: path.join(downloadPath, f.path), length: f.length }))
+      const pieces = Buffer.concat(torrent.info.pieces)
+      // round 0: bulk verify of whatever is on disk; later rounds: only the pieces that were requested again
+      const ok = await verifyOnDisk(files, torrent.pieceLength, pieces)
       for (;;) {
-        const files = torrent.files.map(f => ({ path: path.join(downloadPath, f.path), length: f.length }))
-        const ok = await verifyOnDisk(files, torrent.pieceLength, Buffer.concat(torrent.info.pieces))
         const have = ok.filter(Boolean).length
         await global.telem.emitProgress(id, downloadStage, Math.floor(have / ok.length * 50))
         if (have === ok.length) return
-        if (have === last) {
+        const missing = ok.map((good, i) => good ? -1 : i).filter(i => i >= 0)
+        missing.forEach(i => logger.warn(`Piece ${i} failed verification`))
+        await client.request(torrent, missing, STALL_MS)
+        const again = await verifyOnDisk(files, torrent.pieceLength, pieces, 0, undefined, missing)
+        let repaired = 0
+        for (const i of missing) if (again[i]) { ok[i] = true; repaired++ }
+        if (repaired === 0) { // a round that repaired nothing: the swarm cannot supply these pieces
           const err = new Error('Download stalled.')
           err.code = 'ERRDLSTALL'
           throw err
         }
-        last = have
-        ok.forEach((good, i) => { if (!good) logger.warn(`Piece ${i} failed verification`) })
-        await client.request(torrent, ok.map((good, i) => good ? -1 : i).filter(i => i >= 0), STALL_MS)
       }
     },
     http: async (uri, id, downloadPath, job) => {

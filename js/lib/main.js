@@ -5,7 +5,9 @@
  * `module.exports = async config => termHandler`; stages are loaded by name from this directory, must export
  * a factory, run in order, and each receives the previous result as `job.lastStage`; an error whose code is
  * 'ERRDLSTALL' drops the message (ack), any other error marks the job ERRORED and requeues it (nack).
- * Transport, telemetry and the protobuf codec are injected (`config.queue`, `config.telem`, `config.codec`) —
+ * A job whose `<id>/original/done` object already exists in `triton-staging` skips the stages (lib/main.js:117-124).
+ * Transport, telemetry, the S3 client and the protobuf codec are injected (`config.queue`, `config.telem`,
+ * `config.s3`, `config.codec`) —
  * the AMQP / Prometheus / health-check plumbing of the reference is out of scope here (SURVEY.md §2).
  */
 const path = require('path')
@@ -38,20 +40,37 @@ module.exports = async config => {
     await telem.emitStatus(jobId, STATUS_DOWNLOADING)
     try {
       const table = await loadStages(config, null, logger)
-      let lastStage
-      for (const name of STAGES) lastStage = await table[name](Object.assign(Object.create(job), { lastStage }))
-      await config.queue.publish('v1.convert', config.codec.encodeConvert({ createdAt: new Date().toISOString(), media: job.media }))
-      message.ack()
-    } catch (err) {
-      if (err.code === 'ERRDLSTALL') {
-        message.ack() // dropped, as in the reference
-      } else {
-        await telem.emitStatus(jobId, STATUS_ERRORED)
-        message.nack()
+      // A job whose `done` marker is already in staging was finished by an earlier delivery: skip every stage and
+      // only publish the convert job again (lib/main.js:117-124,153-155) — that is what upload.js writes `done` for.
+      let staged = false
+      try {
+        await config.s3.getObject('triton-staging', path.join(jobId, 'original/', 'done'))
+        staged = true
+      } catch (err) {
+        logger.info('failed to find done file in staging', err && err.message)
       }
-    } finally {
+      if (!staged) {
+        let lastStage = {}
+        for (const name of STAGES) lastStage = await table[name](Object.assign(Object.create(job), { lastStage }))
+      } else {
+        logger.warn('skipping download due to files existing in triton-staging')
+      }
+    } catch (err) {
       active--
+      if (err.code === 'ERRDLSTALL') return message.ack() // dropped, as in the reference
+      await telem.emitStatus(jobId, STATUS_ERRORED)
+      return message.nack()
     }
+    // Outside the stage try/catch, as in the reference (lib/main.js:157-166): a failed publish is logged and the
+    // message is left neither acked nor nacked — it is NOT turned into ERRORED + nack.
+    try {
+      await config.queue.publish('v1.convert', config.codec.encodeConvert({ createdAt: new Date().toISOString(), media: job.media }))
+    } catch (err) {
+      active--
+      return logger.error('failed to create job:', err.message || err)
+    }
+    message.ack()
+    active--
   }
 
   await config.queue.listen('v1.download', handle)

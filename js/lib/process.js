@@ -8,8 +8,13 @@
  */
 const fs = require('fs')
 const path = require('path')
+// One table for this file and for its Python mirror (downloader_b200/stages/process.py), which is the copy that
+// runs against the reference's fixture cases where Node is absent: a rule changed here changes there too.
+const RULES = require('./process_rules.json')
 
-const WANTED = new Set(['.mp4', '.mkv', '.mov', '.webm'])
+const WANTED = new Set(RULES.mediaExts)
+const SKIP_DIR = new RegExp(RULES.skipDirectory.source, RULES.skipDirectory.flags)
+const SEASON_DIR = new RegExp(RULES.seasonDirectory.source, RULES.seasonDirectory.flags)
 const MOVIE = 'MOVIE'
 
 function isMovie (media, enums) {
@@ -17,15 +22,16 @@ function isMovie (media, enums) {
   return media.type === MOVIE || media.type === 1
 }
 
+// lib/process.js:36-67, in the reference's order: only-top-level-directory, movie mode, skip, season
 function wantDirectory (root, full, media, enums) {
   const base = path.basename(full)
-  if (path.dirname(full) === root) {
+  if (RULES.onlyTopLevelDirectoryIsAlwaysEntered && fs.existsSync(path.join(root, base))) {
     const top = fs.readdirSync(root)
     if (top.length === 1 && top[0] === base) return true
   }
-  if (isMovie(media, enums)) return true
-  if (/\/extras|\/commentary/i.test(full)) return false
-  return /s\d+|season/i.test(base)
+  if (RULES.movieModeEntersEveryDirectory && isMovie(media, enums)) return true
+  if (SKIP_DIR.test(full)) return false
+  return SEASON_DIR.test(base)
 }
 
 function collect (root, media, logger, enums) {
@@ -60,7 +66,7 @@ module.exports = async (config, emitter, logger) => {
     const previous = job.lastStage
     logger.info('processing directory', previous.path)
     const files = collect(previous.path, job.media, logger, enums)
-    if (files.length === 0) throw new Error('Failed to find any suitable media files')
+    if (files.length === 0) throw new Error(RULES.noMediaError)
     logger.info('found', files.length, 'media files')
     return { files, downloadPath: previous.path }
   }

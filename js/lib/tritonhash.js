@@ -41,6 +41,28 @@ async function ringAcquire (gpu, bytes, pending = [], collect = () => {}) {
   }
 }
 
+/**
+ * `fh.read` may return fewer bytes than asked for: one read(2) moves at most 0x7ffff000 bytes, and network file
+ * systems return short counts at will.  Reads until `length` bytes are in `buffer`, or the file ends.
+ * onEof 'throw': a short file is an error (an upload must not hash bytes the file does not have);
+ * onEof 'zero':  the missing tail reads as zeros (a verify pass: such a piece simply fails its digest).
+ * The slot is recycled pinned memory — whatever is not written here still holds another slot's bytes.
+ * @returns {Promise<number>} bytes actually read from the file
+ */
+async function readFully (fh, buffer, offset, length, position, onEof = 'throw') {
+  let got = 0
+  while (got < length) {
+    const { bytesRead } = await fh.read(buffer, offset + got, length - got, position + got)
+    if (bytesRead <= 0) break
+    got += bytesRead
+  }
+  if (got < length) {
+    if (onEof === 'throw') throw new Error(`short read: wanted ${length} bytes at ${position}, file ended after ${got}`)
+    buffer.fill(0, offset + got, offset + length)
+  }
+  return got
+}
+
 /** gives back a slot that will not be submitted (e.g. the read that was to fill it failed) */
 function ringRelease (slot) {
   addon.ringRelease(slot)
@@ -76,4 +98,4 @@ function multipartEtag (md5s) {
   return addon.etagCombine(md5s, [n]).toString('hex') + '-' + n
 }
 
-module.exports = { SHA1, MD5, SHA256, init, shutdown, ringAcquire, ringRelease, sha1Batch, partDigests, multipartEtag, stats: () => addon.stats() }
+module.exports = { SHA1, MD5, SHA256, init, shutdown, ringAcquire, ringRelease, readFully, sha1Batch, partDigests, multipartEtag, stats: () => addon.stats() }

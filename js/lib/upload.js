@@ -44,16 +44,19 @@ async function digestParts (file, size, partSize, gpu, slotBytes, mode) {
       const start = first * partSize
       const bytes = Math.min(count * partSize, size - start)
       const { slot, buffer } = await th.ringAcquire(gpu, Math.max(bytes, 16), pending, collect)
-      try {
-        if (bytes > 0) await fd.read(buffer, 0, bytes, start) // straight into pinned memory
-      } catch (err) {
-        th.ringRelease(slot) // an unsubmitted slot would block the ring for good
-        throw err
-      }
       const msgs = []
       for (let k = 0; k < count; k++) msgs.push({ offset: k * partSize, length: Math.min(partSize, size - (first + k) * partSize) })
+      let submitted
+      try {
+        // straight into pinned memory; every byte of every part must come from the file (a file that shrank throws)
+        if (bytes > 0) await th.readFully(fd, buffer, 0, bytes, start, 'throw')
+        submitted = th.partDigests(slot, msgs, { both: true, enableSHA256: mode.enableSHA256 })
+      } catch (err) {
+        th.ringRelease(slot) // a slot that is neither submitted nor released would block the ring for good
+        throw err
+      }
       // a slot's digests arrive one chain latency after its copy (0.25 s for 16 MiB parts): keep reading while they run
-      pending.push(th.partDigests(slot, msgs, { both: true, enableSHA256: mode.enableSHA256 }).then(r => ({ r, first })))
+      pending.push(submitted.then(r => ({ r, first })))
       if (pending.length >= IN_FLIGHT) collect(await pending.shift())
     }
     while (pending.length) collect(await pending.shift())

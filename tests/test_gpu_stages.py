@@ -209,6 +209,68 @@ def test_download_stage_verifies_refetches_and_reports(eng, tmp_path, monkeypatc
         run(stage(Job(media={"id": "m1", "source": SourceType.FILE, "sourceURI": "file:///etc/hostname"})))
 
 
+def test_refetch_rounds_hash_only_the_pieces_that_were_missing(eng, tmp_path):
+    """a refetch round must move about len(missing) x pieceLength over PCIe, not the whole torrent
+    (webtorrent verifies a piece when it completes — the onChunk shape, call site lib/download.js:64-66)."""
+    from downloader_b200 import torrent as tor
+    from downloader_b200.reader import verify_pieces
+    from downloader_b200.stages import Job, SourceType, _NullTelem, download
+    piece = 262144
+    n = 160                                                         # 40 MiB torrent
+    seed_root = tmp_path / "seed"
+    data, blob = _make_torrent(eng, str(seed_root), "show", [("a.mkv", 100 * piece), ("b.mkv", 60 * piece - 777)], piece)
+    meta = tor.parse_metainfo(data, eng)
+    dl = tmp_path / "dl" / "j"
+    os.makedirs(dl / "show")
+    damaged = [3, 4, 99, 100, 159]                                  # incl. the piece that spans both files and the short last one
+    bad = bytearray(blob)
+    for i in damaged:
+        bad[i * piece + 11] ^= 0x40
+    (dl / "show" / "a.mkv").write_bytes(bytes(bad[:100 * piece]))
+    (dl / "show" / "b.mkv").write_bytes(bytes(bad[100 * piece:]))
+    files = meta.on_disk(str(dl))
+    full = verify_pieces(eng, files, piece, meta.pieces)
+    assert np.nonzero(~full["ok"])[0].tolist() == damaged
+    # subset verify: only those pieces cross PCIe, rows come back in the order asked for
+    s0 = eng.stats()
+    sub = verify_pieces(eng, files, piece, meta.pieces, indices=damaged)
+    s1 = eng.stats()
+    moved = s1["h2d_bytes"] - s0["h2d_bytes"]
+    assert not sub["ok"].any() and sub["indices"].tolist() == damaged
+    assert (sub[1] == full[1][damaged]).all()                       # same digests as the bulk pass gave these pieces
+    assert moved < len(damaged) * piece + (64 << 10), moved          # payload + a few KiB of descriptors
+    assert s1["bytes"] - s0["bytes"] == sum(min(piece, len(blob) - i * piece) for i in damaged)
+    with pytest.raises(ValueError):
+        verify_pieces(eng, files, piece, meta.pieces, indices=[5, 5])
+    assert verify_pieces(eng, files, piece, meta.pieces, indices=[])["ok"].size == 0
+    # the stage: round 0 reads everything once, the round after the refetch reads only what was refetched
+    calls = []
+
+    async def fetcher(m, missing, download_path):
+        calls.append(list(missing))
+        for i in missing:
+            lo, hi = i * piece, min((i + 1) * piece, len(blob))
+            for name, start, end in (("a.mkv", 0, 100 * piece), ("b.mkv", 100 * piece, len(blob))):
+                a, b = max(lo, start), min(hi, end)
+                if b > a:
+                    with open(os.path.join(download_path, "show", name), "r+b") as f:
+                        f.seek(a - start)
+                        f.write(blob[a:b])
+
+    tfile = tmp_path / "show.torrent"
+    tfile.write_bytes(data)
+    cfg = {"engine": eng, "fetcher": fetcher, "telem": _NullTelem(), "instance": {"download_path": str(tmp_path / "dl")}}
+    stage = run(download.factory(cfg, {}, Log()))
+    s0 = eng.stats()
+    out = run(stage(Job(media={"id": "j", "source": SourceType.TORRENT, "sourceURI": str(tfile)})))
+    s1 = eng.stats()
+    assert out == {"path": str(dl)} and calls == [damaged]
+    hashed = s1["bytes"] - s0["bytes"]  # round 0: the torrent once; round 1: the refetched pieces; + the bencoded info dict
+    again = sum(min(piece, len(blob) - i * piece) for i in damaged)
+    assert len(blob) + again <= hashed < len(blob) + again + (64 << 10), (hashed, len(blob), again)
+    assert (dl / "show" / "a.mkv").read_bytes() + (dl / "show" / "b.mkv").read_bytes() == blob
+
+
 def test_stage_chain_download_process_upload(eng, tmp_path):
     """lib/main.js:129-140: stages run in order, each receiving the previous result as job.lastStage."""
     from downloader_b200.stages import Job, MediaType, SourceType, _NullTelem, download, process, upload

@@ -167,3 +167,66 @@ def test_s3_mock_plays_the_server():
     etags = [m.putPart("b", "o", uid, i + 1, p, {"x-amz-content-sha256": hashlib.sha256(p).hexdigest()}) for i, p in enumerate(parts)]
     et = m.completeMultipartUpload("b", "o", uid, etags)
     assert et == oracle.etag_multipart(b"".join(hashlib.md5(p).digest() for p in parts))
+
+
+# ---- js/lib/process.js is tied to the mirror that runs ---------------------------------------------
+ROOT = os.path.dirname(HERE)
+RULES_JSON = os.path.join(ROOT, "js", "lib", "process_rules.json")
+REF_PROCESS = "/root/reference/lib/process.js"
+
+
+def test_process_rules_are_one_table_for_js_and_python():
+    """Node is absent, so js/lib/process.js cannot run its fixtures.  Instead both it and the Python mirror (which
+    does run them, above) take every literal from js/lib/process_rules.json: the JS file must hold no extension
+    list or directory regex of its own, and must apply the rules in the reference's order."""
+    import json
+    import re
+    with open(RULES_JSON) as f:
+        rules = json.load(f)
+    assert process_stage.RULES == rules
+    assert list(process_stage.MEDIA_EXTS) == rules["mediaExts"] == [".mp4", ".mkv", ".mov", ".webm"]
+    assert process_stage._RE_SKIP.pattern == "/extras|/commentary" and process_stage._RE_SKIP.flags & re.I
+    assert process_stage._RE_SEASON.pattern == r"s\d+|season" and process_stage._RE_SEASON.flags & re.I
+    with open(os.path.join(ROOT, "js", "lib", "process.js")) as f:
+        js = f.read()
+    code = re.sub(r"/\*.*?\*/", "", js, flags=re.S)
+    code = "\n".join(line.split("//")[0] for line in code.splitlines())
+    assert "require('./process_rules.json')" in code
+    for literal in (".mkv", ".mp4", ".mov", ".webm", "|season", "extras", "commentary", "suitable media files"):
+        assert literal not in code, f"js/lib/process.js carries its own copy of {literal!r}"
+    assert not re.search(r"[=(,]\s*/[^/\n]+/[a-z]*\.test\(", code), "regex literal in js/lib/process.js"
+    # decision order of wantDirectory = lib/process.js:36-67: only top-level dir, movie mode, skip, season
+    body = code[code.index("function wantDirectory"):code.index("function collect")]
+    order = [body.index(k) for k in ("onlyTopLevelDirectoryIsAlwaysEntered", "movieModeEntersEveryDirectory", "SKIP_DIR.test(full)", "SEASON_DIR.test(base)")]
+    assert order == sorted(order)
+    assert "RULES.noMediaError" in code and "new RegExp(RULES.skipDirectory.source, RULES.skipDirectory.flags)" in code
+
+
+@pytest.mark.skipif(not os.path.exists(REF_PROCESS), reason="reference tree not present (GPU box)")
+def test_process_rules_equal_the_reference_literals():
+    """The table's values are the reference's own literals (lib/process.js:15-20,59,64 and the error text, :111)."""
+    import json
+    import re
+    with open(RULES_JSON) as f:
+        rules = json.load(f)
+    with open(REF_PROCESS) as f:
+        ref = f.read()
+    exts = re.findall(r"'(\.[a-z0-9]+)'", ref[ref.index("const mediaExts"):ref.index("]", ref.index("const mediaExts"))])
+    assert exts == rules["mediaExts"]
+    regexes = re.findall(r"if \(/(.+?)/([a-z]*)\.test\((\w+)\)\)", ref)
+    assert regexes == [(rules["skipDirectory"]["source"], rules["skipDirectory"]["flags"], "item"),
+                       (rules["seasonDirectory"]["source"], rules["seasonDirectory"]["flags"], "name")]
+    assert f"throw new Error('{rules['noMediaError']}')" in ref
+
+
+def test_top_level_rule_uses_the_basename_like_the_reference(tmp_path):
+    """lib/process.js:40-45 tests `path.join(absPath, name)`: ANY directory whose basename equals the only top-level
+    entry's name is entered, at any depth — kept as is, in both mirrors."""
+    base = tmp_path / "only"
+    (base / "only").mkdir(parents=True)          # nested directory with the top-level directory's name
+    (base / "only" / "deep.mkv").write_bytes(b"")
+    (base / "other").mkdir()
+    (base / "other" / "no.mkv").write_bytes(b"")
+    p = run(process_stage.factory({}, {}, MockLogger()))
+    res = run(p(Job(lastStage={"path": str(tmp_path)}, media={"id": "x", "type": MediaType.TV})))
+    assert res["files"] == [str(base / "only" / "deep.mkv")]

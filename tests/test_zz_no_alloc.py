@@ -5,9 +5,12 @@ afford cudaMalloc (it synchronises the device and may simply fail).  This entry 
 length-bucketing table inside the library image instead.  The test calls it through the C ABI twice
 in a row — the second batch smaller and differently shaped, so anything left in the shared table by
 the first call would show — and requires bit-exact agreement with the existing launch-level entry
-points (th_sha1_batch / th_md5_batch / th_sha256_batch) on the same device buffers.
+points (th_sha1_batch / th_md5_batch / th_sha256_batch) on the same device buffers, and, first-hand, with
+hashlib on the same bytes.  A third case fills the table to exactly its stated maximum.
 Collected last on purpose (file name), so a failure here cannot hide the other tests' results.
 """
+import hashlib
+
 import numpy as np
 import pytest
 
@@ -16,6 +19,7 @@ pytestmark = pytest.mark.gpu
 SHA1, MD5, SHA256 = 1, 2, 4
 DLEN = {SHA1: 20, MD5: 16, SHA256: 32}
 MAX_MSGS = 65536
+HASHLIB = {SHA1: "sha1", MD5: "md5", SHA256: "sha256"}
 
 
 def _batch(torch, rng, lens):
@@ -66,6 +70,12 @@ def test_no_alloc_entry_point_matches_existing_on_two_calls_in_a_row():
             assert rc == 0
             torch.cuda.synchronize()
             assert (out.cpu().numpy() == ref).all(), (alg, n)
+            # first-hand: the same bytes through hashlib (OpenSSL), not only CUDA against CUDA
+            host, got = data.cpu().numpy(), out.cpu().numpy().reshape(n, DLEN[alg])
+            offs = d_off.cpu().numpy()
+            for i in range(n):
+                m = host[int(offs[i]):int(offs[i]) + lens[i]].tobytes()
+                assert bytes(got[i]) == hashlib.new(HASHLIB[alg], m).digest(), (alg, i, lens[i])
         # SHA-1 with the fused verify: same bitfield as the existing entry point
         exp = torch.from_numpy(_existing(L, torch, SHA1, data, d_off, d_len, n)[0].copy()).cuda()
         bad = sorted({0, n // 2, n - 1})
@@ -83,6 +93,30 @@ def test_no_alloc_entry_point_matches_existing_on_two_calls_in_a_row():
         words = ok.cpu().numpy().view(np.uint32)
         bits = ((words[np.arange(n) >> 5] >> (np.arange(n) & 31)) & 1).astype(bool)
         assert sorted(np.nonzero(~bits)[0].tolist()) == bad
+
+
+def test_no_alloc_entry_point_at_exactly_its_maximum():
+    """n == TH_STATIC_MAX_MSGS fills every slot of the built-in table: accepted, and every digest right."""
+    import torch
+
+    from downloader_b200 import _capi
+    torch.cuda.set_device(0)
+    L = _capi.lib()
+    rng = np.random.default_rng(65536)
+    lens = rng.integers(0, 700, MAX_MSGS).tolist()
+    lens[0], lens[-1], lens[12345] = 70000, 0, 64
+    data, d_off, d_len = _batch(torch, rng, lens)
+    out = torch.zeros(MAX_MSGS * 20, dtype=torch.uint8, device="cuda")
+    rc = L.th_digest_ragged_static(SHA1, data.data_ptr(), d_off.data_ptr(), d_len.data_ptr(), MAX_MSGS, out.data_ptr(),
+                                   None, None, None)
+    assert rc == 0
+    torch.cuda.synchronize()
+    ref, _ = _existing(L, torch, SHA1, data, d_off, d_len, MAX_MSGS)
+    got = out.cpu().numpy()
+    assert (got == ref).all()
+    host, offs, got = data.cpu().numpy(), d_off.cpu().numpy(), got.reshape(MAX_MSGS, 20)
+    for i in list(range(0, MAX_MSGS, 257)) + [0, 12345, MAX_MSGS - 1]:
+        assert bytes(got[i]) == hashlib.sha1(host[int(offs[i]):int(offs[i]) + lens[i]].tobytes()).digest(), i
 
 
 def test_no_alloc_entry_point_refuses_more_than_its_table_holds():
