@@ -192,7 +192,7 @@ def test_process_rules_are_one_table_for_js_and_python():
     code = re.sub(r"/\*.*?\*/", "", js, flags=re.S)
     code = "\n".join(line.split("//")[0] for line in code.splitlines())
     assert "require('./process_rules.json')" in code
-    for literal in (".mkv", ".mp4", ".mov", ".webm", "|season", "extras", "commentary", "suitable media files"):
+    for literal in ("'.mkv'", "'.mp4'", "'.mov'", "'.webm'", "|season", "extras", "commentary", "suitable media files"):
         assert literal not in code, f"js/lib/process.js carries its own copy of {literal!r}"
     assert not re.search(r"[=(,]\s*/[^/\n]+/[a-z]*\.test\(", code), "regex literal in js/lib/process.js"
     # decision order of wantDirectory = lib/process.js:36-67: only top-level dir, movie mode, skip, season
