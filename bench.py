@@ -251,6 +251,13 @@ def make_step(E, data, n, ln, names, outs, expected=None, ok=None):
             rc = L.th_sha256_batch(base, None, None, None, ln, ln, n, outs["sha256"].data_ptr(), sp)
         assert rc == 0, (name, rc)
 
+    if set(names) == {"md5", "sha256"} and L.th_md5_sha256_fused(ln, ln, n) == 1:
+        # few large parts: ONE kernel, the SHA-256 chain's helper warp runs the MD5 chain too (what th_submit launches)
+        def fused_step():
+            rc = L.th_md5_sha256_batch(base, ln, ln, n, outs["md5"].data_ptr(), outs["sha256"].data_ptr(), E.sp)
+            assert rc == 0, rc
+        return fused_step, 1
+
     def step():  # launch order = the runtime's (SHA-1, MD5, SHA-256): the shorter MD5 chains are placed first
         if side:
             ev_fork.record(E.stream)
@@ -261,7 +268,7 @@ def make_step(E, data, n, ln, names, outs, expected=None, ok=None):
             ej.record(s2)
         for ej in ev_join:
             E.stream.wait_event(ej)
-    return step
+    return step, len(names)
 
 
 def time_steps(E, step, steps, warmup):
@@ -529,12 +536,12 @@ def run_workload(E, args, name, algs, n, ln, desc, first_msg, steps, warmup, do_
 
     entry = {"name": name, "config": desc, "algs": algs, "messages_per_gpu": n, "message_bytes": ln,
              "l2": "inputs (%.1f GiB per GPU) exceed the 126 MB L2; no flush" % (total_bytes / 2**30)}
-    step = make_step(E, data, n, ln, names, outs, expected, ok)
+    step, per_step = make_step(E, data, n, ln, names, outs, expected, ok)
     ms, marks = time_steps(E, step, steps, warmup)
     clocks = E.sampler.summary(*marks)
     per_gpu = total_bytes / (ms * 1e-3) / GB
     entry.update({"value": round(E.world * per_gpu, 3), "unit": "GB/s", "ms_per_step": round(ms, 4), "steps": steps,
-                  "warmup": warmup, "gpu_launches": len(names) * steps,
+                  "warmup": warmup, "gpu_launches": per_step * steps,
                   "roofline": roofline_record(E, algs, per_gpu, n, total_bytes, clocks, f"{counters_key}:{algs}" if counters_key else None),
                   "clocks": clocks, "kernel": _plan(algs, ln, n)})
     if variants:
@@ -543,9 +550,10 @@ def run_workload(E, args, name, algs, n, ln, desc, first_msg, steps, warmup, do_
             vn = tuple(v.split("+"))
             if vn == names:
                 continue
-            vms, vmarks = time_steps(E, make_step(E, data, n, ln, vn, outs), steps, warmup)
+            vstep, vper_step = make_step(E, data, n, ln, vn, outs)
+            vms, vmarks = time_steps(E, vstep, steps, warmup)
             vper = total_bytes / (vms * 1e-3) / GB
-            entry["digests"][v] = {"value": round(E.world * vper, 3), "ms_per_step": round(vms, 4), "gpu_launches": len(vn) * steps,
+            entry["digests"][v] = {"value": round(E.world * vper, 3), "ms_per_step": round(vms, 4), "gpu_launches": vper_step * steps,
                                    "roofline": roofline_record(E, v, vper, n, total_bytes, E.sampler.summary(*vmarks),
                                                                f"{counters_key}:{v}" if counters_key else None),
                                    "kernel": _plan(v, ln, n)}
@@ -812,6 +820,8 @@ def _mem_available():
 def _plan(algs, ln, n):
     from downloader_b200 import _capi
     names = algs.split("+")
+    if set(names) == {"md5", "sha256"} and _capi.lib().th_md5_sha256_fused(ln, ln, n) == 1:
+        return "fused: " + _capi.plan(4, ln, ln, n) + "; the helper warp also runs the MD5 chain of the same parts (one launch, parts read once)"
     if len(names) == 1:
         return _capi.plan(ALG_BIT[names[0]], ln, ln, n)
     return {a: _capi.plan(ALG_BIT[a], ln, ln, n) for a in names}

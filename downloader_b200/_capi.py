@@ -93,6 +93,8 @@ def lib() -> C.CDLL:
     L.th_sha1_batch.argtypes = [vp, vp, vp, vp, u64, u64, u32, vp, vp, vp, vp]
     L.th_md5_batch.argtypes = [vp, vp, vp, vp, u64, u64, u32, vp, vp]
     L.th_sha256_batch.argtypes = [vp, vp, vp, vp, u64, u64, u32, vp, vp]
+    L.th_md5_sha256_batch.argtypes = [vp, u64, u64, u32, vp, vp, vp]
+    L.th_md5_sha256_fused.argtypes = [u64, u64, u32]
     L.th_etag_combine_device.argtypes = [vp, vp, u32, vp, vp]
     L.th_synth_fill.argtypes = [vp, u64, u64, u64, u64, u64, vp]
     L.th_digest_ragged_static.argtypes = [u32, vp, vp, vp, u32, vp, vp, vp, vp]

@@ -673,10 +673,17 @@ struct Assist<Sha1> {
 
 // Helper warp: streams the group's message through the TMA tiles (as tile_segment does) and, instead of
 // compressing, expands every block (padding blocks included) into schedule-ring slot (block % SS).
-template <class A, int K, int NST, int SS>
+//
+// MD5_TOO: the helper also runs the MD5 chain of the same messages (hm = its chaining value).  The upload path wants
+// MD5 and SHA-256 of every part (lib/upload.js:45 -> minio getHashSummer), and the helper has the slack: the chain
+// warp needs ~1,850 cycles per block for its 64 rounds, the schedule expansion keeps the helper busy for ~1,200, and
+// an MD5 block is ~260 instructions whose 3-deep dependent chain (latency-bound when it runs alone) interleaves with
+// the expansion's independent work in the same instruction stream.  The block's words are already in the helper's
+// registers, so MD5 costs no second pass over HBM, no second kernel and no sub-partition of its own.
+template <class A, int K, int NST, int SS, bool MD5_TOO = false>
 __device__ __forceinline__ void assist_produce(const void* tmap, uint32_t row0, uint64_t len, uint32_t nch,
                                                uint32_t s_tiles, uint32_t s_bar, uint32_t s_ring, int lane,
-                                               uint32_t one) {
+                                               uint32_t one, uint32_t* hm = nullptr) {
   using G = Tiles<K, NST>;
   constexpr int CH = G::CH;
   constexpr uint32_t SLOT = Assist<A>::WPB * 128;
@@ -716,10 +723,19 @@ __device__ __forceinline__ void assist_produce(const void* tmap, uint32_t row0, 
         uint4 v = lds128(a + (((q0 + q) ^ swz) << 4));
         w[4 * q] = v.x; w[4 * q + 1] = v.y; w[4 * q + 2] = v.z; w[4 * q + 3] = v.w;
       }
-      if (b >= nb) pad_block<A>(w, b - nb, r, len);
+      uint32_t m[16];  // the same block as MD5 sees it: little-endian words, MD5's own padding
+      if (MD5_TOO) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) m[i] = w[i];
+      }
+      if (b >= nb) {
+        pad_block<A>(w, b - nb, r, len);
+        if (MD5_TOO) pad_block<Md5>(m, b - nb, r, len);
+      }
 #pragma unroll
       for (int i = 0; i < 16; i++) w[i] = bswap(w[i]);
       if (produced >= (uint32_t)SS) nb_sync(1 + SS + slot);  // wait until the chain warp has drained this slot
+      if (MD5_TOO) Md5::compress(hm, m, one);                // one basic block with the expansion: ptxas interleaves them
       Assist<A>::expand(w, s_ring + slot * SLOT + lane * 16, one);
       nb_arrive(1 + slot);
       produced++;

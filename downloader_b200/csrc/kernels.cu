@@ -101,6 +101,7 @@ struct TileArgs {
   uint32_t segc;            // sliced kernel: chunks per segment
   uint32_t nseg;            // sliced kernel: segments per message
   uint8_t* out;
+  uint8_t* out_md5;         // chain + helper kernel with MD5_TOO: the MD5 digests the helper warp produces
   const uint8_t* expected;  // SHA-1 only, nullable
   uint32_t* ok_bits;        // SHA-1 only, nullable
   uint32_t one;             // the value 1, opaque to the compiler (see add_fma)
@@ -168,7 +169,8 @@ __global__ void __launch_bounds__(32) digest_tile_kernel(const __grid_constant__
 }
 
 // Few, large messages (fewer groups than SM sub-partitions): chain warp + schedule helper warp per group.
-template <class A, int K, int NST, int SS>
+// MD5_TOO (SHA-256 only): the helper warp also runs the MD5 chain of the same parts (see assist_produce).
+template <class A, int K, int NST, int SS, bool MD5_TOO = false>
 __global__ void __launch_bounds__(64) digest_assist_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs p) {
   extern __shared__ __align__(1024) unsigned char smem[];
   using G = Tiles<K, NST>;
@@ -189,7 +191,13 @@ __global__ void __launch_bounds__(64) digest_assist_kernel(const __grid_constant
   const uint32_t r = (uint32_t)(p.len & 63u);
   const uint32_t total = (uint32_t)(p.len >> 6) + (r < 56 ? 1u : 2u);
   if (warp == 1) {
-    assist_produce<A, K, NST, SS>(&tmap, group * 32u, p.len, nch, s_tiles, s_bar, s_ring, lane, p.one);
+    uint32_t hm[4];
+    Md5::init(hm);
+    assist_produce<A, K, NST, SS, MD5_TOO>(&tmap, group * 32u, p.len, nch, s_tiles, s_bar, s_ring, lane, p.one, hm);
+    if (MD5_TOO) {
+      const uint32_t idx = group * 32u + lane;
+      if (idx < p.n) store_digest<Md5>(p.out_md5 + (size_t)idx * Md5::DLEN, hm);
+    }
   } else {
     uint32_t h[A::NS];
     A::init(h);
@@ -445,6 +453,7 @@ struct TileOpts {
   int sliced_min_groups = 592;  // auto: use the sliced kernel from this many 32-message groups
   int tile_many_groups = 8192;  // auto: SHA-1 / SHA-256 batches with at least this many groups go back to one-warp CTAs
                                 // (many waves balance themselves and measured 1-12 % faster than the persistent kernel)
+  int fuse_md5_sha256 = 1;      // th_md5_sha256_batch: 1 = one chain + helper kernel does both where the plan is "assist"
   int ragged_rows = 1;          // per-lane kernels: 1 = cooperative cp.async row tiles, 0 = one bulk copy per lane
   int rows_variant[3] = {2, 2, 2};  // index into g_rows_variants per digest
 };
@@ -477,13 +486,13 @@ cudaError_t launch_sliced(const CUtensorMap& m, const TileArgs& a, uint32_t grid
   return cudaGetLastError();
 }
 
-template <class A, int K, int NST, int SS>
+template <class A, int K, int NST, int SS, bool MD5_TOO = false>
 cudaError_t launch_assist(const CUtensorMap& m, const TileArgs& a, uint32_t grid, uint32_t, size_t pad, cudaStream_t st) {
   constexpr int smem = Tiles<K, NST>::WARP_BYTES + SS * Assist<A>::WPB * 128 + 8 * NST;
   static bool done[64] = {};
-  cudaError_t e0 = allow_smem(digest_assist_kernel<A, K, NST, SS>, done, smem > kRoomySmem ? smem : kRoomySmem);
+  cudaError_t e0 = allow_smem(digest_assist_kernel<A, K, NST, SS, MD5_TOO>, done, smem > kRoomySmem ? smem : kRoomySmem);
   if (e0 != cudaSuccess) return e0;
-  digest_assist_kernel<A, K, NST, SS><<<grid, 64, pad > (size_t)smem ? pad : (size_t)smem, st>>>(m, a);
+  digest_assist_kernel<A, K, NST, SS, MD5_TOO><<<grid, 64, pad > (size_t)smem ? pad : (size_t)smem, st>>>(m, a);
   return cudaGetLastError();
 }
 
@@ -561,13 +570,16 @@ static Plan make_plan(int ai, uint64_t stride, uint64_t len, uint32_t n) {
 }
 
 // Returns TH_OK if launched, 1 if this batch is not eligible (caller falls back to the bulk-copy kernel).
+// d_out_md5 != nullptr (ai == 2 only): MD5 digests as well, from the helper warp — only the assist plan can do that;
+// returns 1 for any other plan.
 static int launch_uniform(int ai, const void* d_base, uint64_t stride, uint64_t len, uint32_t n, uint8_t* d_out,
-                          const uint8_t* d_expected, uint32_t* d_ok_bits, cudaStream_t st) {
+                          const uint8_t* d_expected, uint32_t* d_ok_bits, cudaStream_t st, uint8_t* d_out_md5 = nullptr) {
   const Plan pl = make_plan(ai, stride, len, n);
   if (pl.path == 1) return 1;
+  if (d_out_md5 && (pl.path != 4 || ai != 2)) return 1;
   CUtensorMap tmap;
   if (!make_tmap(&tmap, d_base, len, stride, n)) return 1;
-  TileArgs a{len, n, pl.segc, pl.nseg, d_out, d_expected, d_ok_bits, 1u, 0u};
+  TileArgs a{len, n, pl.segc, pl.nseg, d_out, d_out_md5, d_expected, d_ok_bits, 1u, 0u};
   uint32_t grid = pl.grid;
   size_t pad = 0;
   if (pl.path != 3) {  // few CTAs: pad to one per SM and rotate by a per-launch salt (see spread_group)
@@ -580,6 +592,10 @@ static int launch_uniform(int ai, const void* d_base, uint64_t stride, uint64_t 
       grid = (uint32_t)sms;
       pad = kRoomySmem;
     }
+  }
+  if (pl.path == 4 && d_out_md5) {
+    const cudaError_t e = launch_assist<Sha256, 2, 2, 4, true>(tmap, a, grid, 64, pad, st);
+    return e == cudaSuccess ? TH_OK : TH_ECUDA;
   }
   if (pl.path == 4) {
     cudaError_t e;
@@ -717,6 +733,26 @@ int th_sha256_batch(const void* d_base, const uint64_t* d_offsets, const uint64_
                            nullptr, nullptr, stream);
 }
 
+int th_md5_sha256_fused(uint64_t stride, uint64_t len, uint32_t n) {
+  if (!th::g_opts.fuse_md5_sha256 || n == 0) return 0;
+  return th::make_plan(2, stride, len, n).path == 4 ? 1 : 0;
+}
+
+int th_md5_sha256_batch(const void* d_base, uint64_t stride, uint64_t len, uint32_t n, uint8_t* d_out16,
+                        uint8_t* d_out32, void* stream) {
+  if (!d_out16 || !d_out32) return TH_EINVAL;
+  if (n == 0) return TH_OK;
+  if (!d_base) return TH_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(d_base) & 15) != 0 || ((stride & 15) != 0 && n > 1)) return TH_EALIGN;
+  if (len >= (1ull << 37)) return TH_ETOOBIG;
+  if (th_md5_sha256_fused(stride, len, n)) {
+    const int rc = th::launch_uniform(2, d_base, stride, len, n, d_out32, nullptr, nullptr, static_cast<cudaStream_t>(stream), d_out16);
+    if (rc <= 0) return rc;
+  }
+  const int rc = th_md5_batch(d_base, nullptr, nullptr, nullptr, stride, len, n, d_out16, stream);
+  return rc != TH_OK ? rc : th_sha256_batch(d_base, nullptr, nullptr, nullptr, stride, len, n, d_out32, stream);
+}
+
 int th_etag_combine_device(const uint8_t* d_md5s, const uint64_t* d_part_prefix, uint32_t n_objects,
                            uint8_t* d_out16, void* stream) {
   if (!d_part_prefix || !d_out16) return TH_EINVAL;
@@ -793,6 +829,7 @@ int th_set_option(const char* name, long long value) {
   if (k == "tile_many_groups") { if (value < 1) return TH_EINVAL; th::g_opts.tile_many_groups = (int)value; return TH_OK; }
   if (k == "sliced_min_groups") { if (value < 1) return TH_EINVAL; th::g_opts.sliced_min_groups = (int)value; return TH_OK; }
   if (k == "ragged_rows") { if (value < 0 || value > 1) return TH_EINVAL; th::g_opts.ragged_rows = (int)value; return TH_OK; }
+  if (k == "fuse_md5_sha256") { if (value < 0 || value > 1) return TH_EINVAL; th::g_opts.fuse_md5_sha256 = (int)value; return TH_OK; }
   if (k == "rows_variant") {
     if (value < 0 || value >= th::kNumRowsVariants) return TH_EINVAL;
     for (int a = 0; a < 3; a++) th::g_opts.rows_variant[a] = (int)value;

@@ -38,7 +38,7 @@
 
 namespace {
 
-constexpr size_t kRingAlign = 256;
+constexpr size_t kRingAlign = 4096;  // slots start on a page: O_DIRECT reads can land in them (reader.py)
 constexpr int kGpuBits = 6;  // ids = (sequence << 6) | index of the GPU in its context
 constexpr int kMaxGpus = 1 << kGpuBits;
 
@@ -91,7 +91,7 @@ struct Ticket {
   // One entry per launch item: the end of its kernel (timing) and of its digest copy-back.  A ticket is joined
   // on the HOST over these events — never by one stream waiting for another: a stream parked on an event of a
   // 0.25..1 s chain also parks every stream that shares its hardware queue (120 streams share 32 queues).
-  struct Tail { cudaEvent_t k_end; cudaEvent_t done; int alg; };
+  struct Tail { cudaEvent_t k_end; cudaEvent_t done; int alg; bool also_md5; };  // also_md5: a fused MD5 + SHA-256 launch
   std::vector<Tail> tails;
   std::atomic<int> cb_left{0};  // launch items that have not reached their host function yet
   cudaEvent_t ev_ready = nullptr;  // inputs (payload + descriptors) on the device; timing-enabled when timing is on
@@ -551,10 +551,21 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
   const bool sha1_verify = (mask & 1u) && expected;
   const ItemList plain = build_items(false);
   const ItemList verified = sha1_verify ? build_items(true) : ItemList{};
+  // MD5 and SHA-256 of the same few large messages (parts of an upload) share ONE kernel: the helper warp of the
+  // SHA-256 chain runs the MD5 chain too (kernels.cu, MD5_TOO).  Such an item is launched in the SHA-256 pass only.
+  const bool both = (mask & TH_ALG_MD5) && (mask & TH_ALG_SHA256);
+  auto item_len = [&](const Item& it) { return it.kind == 1 ? msgs[it.first].length : ulen; };
+  auto item_stride = [&](const Item& it) { return it.kind == 1 ? ((msgs[it.first].length + 15) & ~15ull) : ustride; };
+  auto fused = [&](const Item& it) {
+    return both && it.kind != 2 && th_md5_sha256_fused(item_stride(it), item_len(it), (uint32_t)it.cnt) == 1;
+  };
   const uint64_t sets = (uint64_t)(timing ? std::min(g.n_sets, kTimedStreamSets) : g.n_sets);
   int n_items = 0;
-  for (int a = 0; a < 3; a++)
-    if (mask & (1u << a)) n_items += (int)((a == 0 && sha1_verify) ? verified : plain).items.size();
+  for (int a = 0; a < 3; a++) {
+    if (!(mask & (1u << a))) continue;
+    for (const Item& it : ((a == 0 && sha1_verify) ? verified : plain).items)
+      if (!(a == 1 && fused(it))) n_items++;
+  }
   t->cb_left.store(n_items);
   t->tails.reserve((size_t)n_items);
 
@@ -572,10 +583,13 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
     const ItemList& il = (a == 0 && sha1_verify) ? verified : plain;
     const size_t ragged_skip = il.skip;  // leading entries of the order that are launched alone
     const std::vector<Item>& items = il.items;
+    bool first_launch = true;
     for (size_t k = 0; k < items.size() && rc == TH_OK; k++) {
       const Item& it = items[k];
+      if (a == 1 && fused(it)) continue;  // its MD5 comes out of the SHA-256 pass's fused launch
+      const bool with_md5 = a == 2 && fused(it);
       cudaStream_t ps = st;
-      if (k > 0 && !(it.kind == 2 && d_ok && use_order)) {  // (the bitfield memset above is ordered on st only)
+      if (!first_launch && !(it.kind == 2 && d_ok && use_order)) {  // (the bitfield memset above is ordered on st only)
         ps = g.sets[g.next_stream[a]++ % sets].alg[a];
         CU(c, cudaStreamWaitEvent(ps, ev_in, 0));
       }
@@ -585,10 +599,13 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
       const uint64_t* po = it.kind == 2 ? d_off : nullptr;
       const uint64_t* pl = it.kind == 2 ? d_len : nullptr;
       const uint32_t* pr = it.kind == 2 && d_ord ? d_ord + ragged_skip : nullptr;
+      first_launch = false;
       const uint64_t pstride = lone ? ((msgs[first].length + 15) & ~15ull) : ustride;
       const uint64_t plen = lone ? msgs[first].length : ulen;
       uint8_t* o = d_out + first * dlen[a];
-      if (a == 0)
+      if (with_md5)
+        rc = th_md5_sha256_batch(pb, pstride, plen, (uint32_t)it.cnt, jb->d + out_off[1] + first * 16, o, ps);
+      else if (a == 0)
         rc = th_sha1_batch(pb, po, pl, pr, pstride, plen, (uint32_t)it.cnt, o, d_exp ? d_exp + first * 20 : nullptr,
                            d_ok ? d_ok + first / 32 : nullptr, ps);
       else if (a == 1)
@@ -597,7 +614,7 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
         rc = th_sha256_batch(pb, po, pl, pr, pstride, plen, (uint32_t)it.cnt, o, ps);
       if (rc != TH_OK) break;
       g.st.launches += 1;
-      Ticket::Tail tl{nullptr, nullptr, a};
+      Ticket::Tail tl{nullptr, nullptr, a, with_md5};
       if (timing) {
         CU(c, cudaEventCreate(&tl.k_end));
         CU(c, cudaEventRecord(tl.k_end, ps));
@@ -619,6 +636,10 @@ int enqueue(th_ctx* c, Gpu& g, Ticket* t, const uint8_t* d_base, Slot* slot, con
           g.st.d2h_bytes += (hole - lo) * dlen[a];
         }
         lo = hole + 1;
+      }
+      if (with_md5) {  // the MD5 digests the same launch produced
+        CU(c, cudaMemcpyAsync(jb->h + out_off[1] + first * 16, jb->d + out_off[1] + first * 16, it.cnt * 16, cudaMemcpyDeviceToHost, ps));
+        g.st.d2h_bytes += it.cnt * 16;
       }
       if (d_ok) {  // the bitfield words this item produced (items split on word boundaries)
         const size_t w0 = first / 32, w1 = (first + span + 31) / 32;
@@ -965,7 +986,7 @@ static Ticket* wait_ticket(th_ctx* c, Gpu& g, std::unique_lock<std::mutex>& lk, 
       if (!t->ev_k0[a]) continue;
       if (cudaEventElapsedTime(&ms, g.ev_epoch, t->ev_k0[a]) == cudaSuccess) t->times_ms[1 + 2 * a] = ms;
       for (auto& tl : t->tails)  // a digest ends when the last of its launch items does
-        if (tl.alg == a && tl.k_end && cudaEventElapsedTime(&ms, g.ev_epoch, tl.k_end) == cudaSuccess)
+        if ((tl.alg == a || (a == 1 && tl.also_md5)) && tl.k_end && cudaEventElapsedTime(&ms, g.ev_epoch, tl.k_end) == cudaSuccess)
           t->times_ms[2 + 2 * a] = std::max(t->times_ms[2 + 2 * a], (double)ms);
       if (t->times_ms[1 + 2 * a] >= 0 && t->times_ms[2 + 2 * a] >= 0) g.st.kernel_ms += t->times_ms[2 + 2 * a] - t->times_ms[1 + 2 * a];
     }

@@ -18,29 +18,47 @@ from ._capi import ALG_MD5, ALG_SHA1, ALG_SHA256, DIGEST_LEN
 
 READ_CHUNK = 16 << 20
 READ_THREADS = max(1, min(16, int(os.environ.get("TRITONHASH_READ_THREADS", "0")) or (os.cpu_count() or 1)))
-_POOL = None
+DIRECT_ALIGN = 4096   # O_DIRECT wants memory address, file offset and length aligned to the logical block size
+_POOLS: Dict[int, object] = {}
 
 
-def _pool():
-    global _POOL
-    if _POOL is None:
+def _pool(gpu: int = 0):
+    """One reader pool per GPU ring: with several GPUs every ring has its own readers, so a feeder that is waiting
+    for a slow read does not hold up the reads that fill another GPU's slots."""
+    pool = _POOLS.get(gpu)
+    if pool is None:
         from concurrent.futures import ThreadPoolExecutor
-        _POOL = ThreadPoolExecutor(max_workers=READ_THREADS, thread_name_prefix="tritonhash-read")
-    return _POOL
+        pool = _POOLS[gpu] = ThreadPoolExecutor(max_workers=READ_THREADS, thread_name_prefix=f"tritonhash-read-gpu{gpu}")
+    return pool
 
 
 def _align(x: int, a: int) -> int:
     return (x + a - 1) // a * a
 
 
-class _ConcatFiles:
-    """The torrent's view of a download directory: files laid end to end ([dep] fs-chunk-store)."""
+def _direct_default() -> bool:
+    return os.environ.get("TRITONHASH_O_DIRECT", "0") == "1"
 
-    def __init__(self, files: Sequence[Tuple[str, int]]):
+
+class _ConcatFiles:
+    """The torrent's view of a download directory: files laid end to end ([dep] fs-chunk-store).
+
+    direct=True reads with O_DIRECT where it can: a staged media file is read once, front to back, and is usually
+    larger than what is worth keeping in the page cache — buffered reads copy every byte twice (disk -> page cache ->
+    pinned slot) and evict everything else.  With O_DIRECT the device DMA lands in the pinned ring slot itself.  The
+    aligned body of each chunk (4 KiB-aligned slot address, file offset and length; ring slots are 4 KiB-aligned)
+    goes through the O_DIRECT descriptor, the unaligned head / tail bytes and file systems that refuse O_DIRECT
+    (tmpfs) through the ordinary one."""
+
+    def __init__(self, files: Sequence[Tuple[str, int]], direct: Optional[bool] = None):
         self.files = [(p, int(n)) for p, n in files]
         self.starts = np.cumsum([0] + [n for _, n in self.files]).tolist()
         self.total = self.starts[-1]
+        self.direct = _direct_default() if direct is None else bool(direct)
         self._fds: Dict[int, int] = {}
+        self._dfds: Dict[int, int] = {}
+        self.direct_bytes = 0      # bytes that came through O_DIRECT descriptors
+        self.buffered_bytes = 0    # bytes that came through the page cache
 
     def _fd(self, i: int) -> int:
         fd = self._fds.get(i)
@@ -52,23 +70,50 @@ class _ConcatFiles:
             self._fds[i] = fd
         return fd
 
+    def _dfd(self, i: int) -> int:
+        if not self.direct:
+            return -1
+        fd = self._dfds.get(i)
+        if fd is None:
+            try:
+                fd = os.open(self.files[i][0], os.O_RDONLY | os.O_DIRECT)
+            except (OSError, AttributeError):  # tmpfs and some network file systems refuse O_DIRECT
+                fd = -1
+            self._dfds[i] = fd
+        return fd
+
     @staticmethod
-    def _pread_chunk(fd: int, view: np.ndarray, off: int) -> None:
-        """preadv straight into the (pinned) view; what the file does not supply reads as zeros."""
-        take, got = view.size, 0
+    def _pread_all(fd: int, mv: memoryview, off: int) -> int:
+        got = 0
+        while got < len(mv):
+            r = os.preadv(fd, [mv[got:]], off + got)
+            if r <= 0:
+                break
+            got += r
+        return got
+
+    def _pread_chunk(self, fd: int, dfd: int, view: np.ndarray, off: int) -> Tuple[int, int]:
+        """preadv straight into the (pinned) view; what the file does not supply reads as zeros.
+        Returns (bytes read with O_DIRECT, bytes read through the page cache)."""
+        take, got, direct = view.size, 0, 0
         if fd >= 0:
             mv = memoryview(view)
-            while got < take:
-                r = os.preadv(fd, [mv[got:]], off + got)
-                if r <= 0:
-                    break
-                got += r
+            body = take // DIRECT_ALIGN * DIRECT_ALIGN
+            if dfd >= 0 and body and off % DIRECT_ALIGN == 0 and view.ctypes.data % DIRECT_ALIGN == 0:
+                try:
+                    direct = self._pread_all(dfd, mv[:body], off)  # short only at the end of the file
+                except OSError:
+                    direct = 0                                      # e.g. EINVAL from a stacked file system
+                got = direct
+            if got < take and (direct == 0 or got == body):
+                got += self._pread_all(fd, mv[got:], off + got)
         if got < take:
             view[got:] = 0
+        return direct, got - direct
 
-    def readinto(self, view: np.ndarray, pos: int) -> None:
+    def readinto(self, view: np.ndarray, pos: int, gpu: int = 0) -> None:
         """Fill `view` with stream bytes [pos, pos+len(view)); missing / short files read as zeros.
-        Large ranges are cut into READ_CHUNK pieces read by a small thread pool (preadv releases the GIL): one
+        Large ranges are cut into READ_CHUNK pieces read by that GPU's thread pool (preadv releases the GIL): one
         thread copies from the page cache at a few GB/s, an order of magnitude below what the H2D link takes."""
         n = view.size
         done = 0
@@ -79,26 +124,27 @@ class _ConcatFiles:
             off = pos + done - self.starts[i]
             take = min(n - done, flen - off)
             if take > 0:
-                fd = self._fd(i)
+                fd, dfd = self._fd(i), self._dfd(i)
                 for c in range(0, take, READ_CHUNK):
                     m = min(READ_CHUNK, take - c)
-                    jobs.append((fd, view[done + c:done + c + m], off + c))
+                    jobs.append((fd, dfd, view[done + c:done + c + m], off + c))
                 done += take
             i += 1
         if done < n:
             view[done:] = 0
         if len(jobs) > 1 and READ_THREADS > 1:
-            for f in [_pool().submit(self._pread_chunk, *j) for j in jobs]:
-                f.result()
+            counts = [f.result() for f in [_pool(gpu).submit(self._pread_chunk, *j) for j in jobs]]
         else:
-            for j in jobs:
-                self._pread_chunk(*j)
+            counts = [self._pread_chunk(*j) for j in jobs]
+        self.direct_bytes += sum(c[0] for c in counts)
+        self.buffered_bytes += sum(c[1] for c in counts)
 
     def close(self) -> None:
-        for fd in self._fds.values():
+        for fd in list(self._fds.values()) + list(self._dfds.values()):
             if fd >= 0:
                 os.close(fd)
         self._fds.clear()
+        self._dfds.clear()
 
 
 def _slots_in_flight(engine, batch_bytes: int, in_flight: Optional[int]) -> int:
@@ -145,10 +191,10 @@ def _stream_messages(engine, src: _ConcatFiles, bounds: Sequence[Tuple[int, int]
         contiguous = all(bounds[k + 1][0] == bounds[k][1] and (bounds[k][1] - bounds[k][0]) % 16 == 0 for k in range(i, j - 1))
         try:  # an acquired slot that is neither submitted nor released would block the FIFO ring for good
             if contiguous:  # pieces / parts back to back: one sequential read for the whole slot
-                src.readinto(view[:bounds[j - 1][1] - bounds[i][0]], bounds[i][0])
+                src.readinto(view[:bounds[j - 1][1] - bounds[i][0]], bounds[i][0], gpu)
             else:
                 for k in range(i, j):
-                    src.readinto(view[offs[k - i]:offs[k - i] + lens[k - i]], bounds[k][0])
+                    src.readinto(view[offs[k - i]:offs[k - i] + lens[k - i]], bounds[k][0], gpu)
             exp = expected_sha1[i:j] if expected_sha1 is not None else None
             ticket = engine.submit(slot, np.array(offs, np.uint64), np.array(lens, np.uint64), algs, exp)
         except BaseException:
@@ -163,10 +209,11 @@ def _stream_messages(engine, src: _ConcatFiles, bounds: Sequence[Tuple[int, int]
 
 
 def hash_file_parts(engine, path: str, ranges: Sequence[Tuple[int, int]], algs: int = ALG_MD5 | ALG_SHA256, gpu: int = 0,
-                    batch_bytes: int = 256 << 20, in_flight: Optional[int] = None) -> dict:
-    """Per-part digests of one file (minio's first pass over every part, all parts in a few launches)."""
+                    batch_bytes: int = 256 << 20, in_flight: Optional[int] = None, direct: Optional[bool] = None) -> dict:
+    """Per-part digests of one file (minio's first pass over every part, all parts in a few launches).
+    direct: read with O_DIRECT (default: TRITONHASH_O_DIRECT=1), see _ConcatFiles."""
     size = os.path.getsize(path)
-    src = _ConcatFiles([(path, size)])
+    src = _ConcatFiles([(path, size)], direct)
     try:
         return _stream_messages(engine, src, list(ranges), algs, None, gpu, batch_bytes, in_flight)
     finally:
@@ -179,7 +226,8 @@ def piece_bounds(total: int, piece_length: int) -> List[Tuple[int, int]]:
 
 
 def verify_pieces(engine, files: Sequence[Tuple[str, int]], piece_length: int, expected_sha1, gpu: int = 0,
-                  batch_bytes: int = 256 << 20, in_flight: Optional[int] = None, indices: Optional[Sequence[int]] = None) -> dict:
+                  batch_bytes: int = 256 << 20, in_flight: Optional[int] = None, indices: Optional[Sequence[int]] = None,
+                  direct: Optional[bool] = None) -> dict:
     """Bulk re-verify of an on-disk download ([dep] webtorrent `_verifyPieces`): returns {'ok': bool[n]
     (the bitfield), ALG_SHA1: digests}.  Missing files hash as zeros and simply fail verification.
 
@@ -187,7 +235,7 @@ def verify_pieces(engine, files: Sequence[Tuple[str, int]], piece_length: int, e
     lib/download.js:64-66): after a refetch only the pieces that were requested again are read, copied and hashed,
     not the whole download.  expected_sha1 stays the full info.pieces table; 'ok' and the digests then have one row
     per requested index, in that order ('indices' echoes them)."""
-    src = _ConcatFiles(files)
+    src = _ConcatFiles(files, direct)
     bounds = piece_bounds(src.total, piece_length)
     exp = np.ascontiguousarray(expected_sha1, np.uint8).reshape(-1, 20)
     if exp.shape[0] != len(bounds):
@@ -211,7 +259,8 @@ def verify_pieces(engine, files: Sequence[Tuple[str, int]], piece_length: int, e
 
 
 def hash_media_file(engine, path: str, piece_length: int, expected_sha1, part_ranges: Sequence[Tuple[int, int]],
-                    part_algs: int = ALG_MD5 | ALG_SHA256, gpu: int = 0, batch_bytes: int = 512 << 20, in_flight: Optional[int] = None) -> dict:
+                    part_algs: int = ALG_MD5 | ALG_SHA256, gpu: int = 0, batch_bytes: int = 512 << 20, in_flight: Optional[int] = None,
+                    direct: Optional[bool] = None) -> dict:
     """One pass over a staged media file feeding BOTH consumers of its bytes: SHA-1 by torrent piece (with
     the fused verify) and MD5 / SHA-256 by S3 part.  Each ring slot is read once, crosses PCIe once, and is
     submitted twice (th_submit allows that).  Slots hold whole parts, and parts are multiples of the piece
@@ -227,7 +276,7 @@ def hash_media_file(engine, path: str, piece_length: int, expected_sha1, part_ra
     for s0, e0 in part_ranges:  # checked before any slot is taken: a slot holds whole pieces and whole parts
         if s0 % piece_length or (e0 % piece_length and e0 != size):
             raise ValueError("part boundaries must be multiples of the piece length")
-    src = _ConcatFiles([(path, size)])
+    src = _ConcatFiles([(path, size)], direct)
     pending: List[tuple] = []
     in_flight = _slots_in_flight(engine, batch_bytes, in_flight)
 
@@ -255,7 +304,7 @@ def hash_media_file(engine, path: str, piece_length: int, expected_sha1, part_ra
             slot, view = engine.ring_acquire(max(end - start, 16), gpu)
             tp = None
             try:
-                src.readinto(view[:end - start], start)
+                src.readinto(view[:end - start], start, gpu)
                 p0, p1 = start // piece_length, -(-end // piece_length)
                 offs = np.array([pb[i][0] - start for i in range(p0, p1)], np.uint64)
                 lens = np.array([pb[i][1] - pb[i][0] for i in range(p0, p1)], np.uint64)
@@ -274,4 +323,39 @@ def hash_media_file(engine, path: str, piece_length: int, expected_sha1, part_ra
         drain(0)
     finally:
         src.close()
-    return {"pieces": pieces, "parts": parts}
+    return {"pieces": pieces, "parts": parts, "read": {"direct_bytes": src.direct_bytes, "buffered_bytes": src.buffered_bytes}}
+
+
+def hash_media_files(engine, jobs: Sequence[dict], gpus: Optional[Sequence[int]] = None) -> List[dict]:
+    """Several staged media files over several GPUs of ONE context — the files loop of lib/upload.js:34-52, which the
+    reference runs strictly one file after the other.  Files are dealt to the GPUs by bytes (sharding.shard_by_bytes);
+    every GPU has its own feeder thread, its own ring and its own reader pool, so the GPUs' reads, copies and chains
+    overlap and no feeder waits on another GPU's ring (the library takes one lock per GPU).
+    jobs: dicts of hash_media_file's arguments (path, piece_length, expected_sha1, part_ranges, ...).
+    Returns hash_media_file's results in the order of `jobs`, each with the 'gpu' that hashed it."""
+    import threading
+
+    from .sharding import shard_by_bytes
+    gpus = list(gpus) if gpus is not None else list(range(len(getattr(engine, "gpu_ids", [0]))))
+    sizes = [os.path.getsize(j["path"]) for j in jobs]
+    shards = shard_by_bytes(sizes, len(gpus))
+    out: List[Optional[dict]] = [None] * len(jobs)
+    errors: List[BaseException] = []
+
+    def feeder(k: int) -> None:
+        try:
+            for i in shards[k]:
+                r = hash_media_file(engine, gpu=gpus[k], **jobs[i])
+                r["gpu"] = gpus[k]
+                out[i] = r
+        except BaseException as e:  # noqa: BLE001 — re-raised in the caller's thread
+            errors.append(e)
+
+    threads = [threading.Thread(target=feeder, args=(k,), name=f"tritonhash-feed-gpu{gpus[k]}") for k in range(len(gpus))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    if errors:
+        raise errors[0]
+    return out  # type: ignore[return-value]

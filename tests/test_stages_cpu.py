@@ -230,3 +230,42 @@ def test_top_level_rule_uses_the_basename_like_the_reference(tmp_path):
     p = run(process_stage.factory({}, {}, MockLogger()))
     res = run(p(Job(lastStage={"path": str(tmp_path)}, media={"id": "x", "type": MediaType.TV})))
     assert res["files"] == [str(base / "only" / "deep.mkv")]
+
+
+def _aligned_u8(n, align=4096):
+    raw = np.zeros(n + align, np.uint8)
+    off = (-raw.ctypes.data) % align
+    return raw[off:off + n]
+
+
+def test_o_direct_reads_give_the_same_bytes_as_buffered_reads(tmp_path):
+    """reader._ConcatFiles(direct=True): the 4 KiB-aligned body of a chunk goes through an O_DIRECT descriptor, the
+    unaligned head / tail and file systems without O_DIRECT through the page cache.  Whatever the mix, the bytes in
+    the slot are the file's bytes, missing tails are zeros, and the two byte counters add up to what was read."""
+    rng = np.random.default_rng(4096)
+    sizes = [3 * 4096 * 700 + 1234, 0, 4096 * 5, 777]
+    files, blob = [], b""
+    for i, n in enumerate(sizes):
+        p = tmp_path / f"f{i}.bin"
+        data = rng.integers(0, 256, n, dtype=np.uint8).tobytes()
+        p.write_bytes(data)
+        blob += data
+        files.append((str(p), n))
+    total = len(blob)
+    for direct in (False, True):
+        src = _ConcatFiles(files, direct=direct)
+        try:
+            for pos, n in [(0, total), (4096, 4096 * 600), (4096 * 3, 4096 * 10 + 5), (17, 50000), (total - 100, 300)]:
+                view = _aligned_u8(n)
+                view[:] = 0xAA
+                src.readinto(view, pos)
+                want = blob[pos:pos + n] + bytes(max(0, pos + n - total))
+                assert view.tobytes() == want, (direct, pos, n)
+            assert src.direct_bytes + src.buffered_bytes == sum(min(n, total - pos) for pos, n in
+                                                                 [(0, total), (4096, 4096 * 600), (4096 * 3, 4096 * 10 + 5), (17, 50000), (total - 100, 300)])
+            if not direct:
+                assert src.direct_bytes == 0
+            elif src._dfds and any(fd >= 0 for fd in src._dfds.values()):
+                assert src.direct_bytes > 0  # this file system takes O_DIRECT: the aligned bodies used it
+        finally:
+            src.close()
