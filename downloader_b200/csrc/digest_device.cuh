@@ -562,6 +562,84 @@ __device__ __forceinline__ void tile_segment(const void* tmap, uint32_t row0, ui
   }
 }
 
+// The same stream for a warp that runs ALONE on its sub-partition (few large messages, MD5): a lone MD5 chain is
+// latency-bound — its step is a 3-deep dependent chain, 12.1 clocks, of which only 4 issue slots are used — so everything
+// else a block needs (four LDS.128, the swizzled addresses, the tail tests, and once per stage the barrier wait and the
+// next TMA issue) is free IF it sits in the same basic block as a compression and does not feed it.  tile_segment loads
+// a block and then compresses it, so all of that is serial: 968 clocks per block measured against 807 for the bare
+// compression (tools/microbench/chain.cu).  Here block b+1 is loaded into a second register set before block b is
+// compressed (two blocks per loop trip, ping-pong, no register moves); moving on to the next stage happens inside that
+// prefetch, i.e. one block early, which also hands the stage back to the TMA unit one block sooner.
+template <class A, int K, int NST>
+__device__ __forceinline__ void tile_stream_prefetch(const void* tmap, uint32_t row0, uint64_t len, uint32_t nch, uint32_t* h,
+                                                     uint32_t s_tiles, uint32_t s_bar, int lane, uint32_t one) {
+  using G = Tiles<K, NST>;
+  constexpr int CH = G::CH;
+  constexpr uint32_t BPC = 2 * K;  // 64-byte blocks per chunk (= per pipeline stage)
+  auto issue = [&](uint32_t c, int s) {
+    if (lane == 0) {
+      const uint64_t pos = (uint64_t)c * CH;
+      const uint64_t left = pos < len ? len - pos : 0;
+      const uint32_t ntile = left >= (uint64_t)CH ? (uint32_t)K : (uint32_t)((left + 127) >> 7);
+      const uint32_t bar = s_bar + 8 * s;
+      mbar_arrive_expect_tx(bar, ntile * G::TILE);
+#pragma unroll
+      for (int j = 0; j < K; j++)
+        if ((uint32_t)j < ntile) tma_tile_2d(s_tiles + (s * K + j) * G::TILE, tmap, (uint32_t)pos + 128u * j, row0, bar);
+    }
+  };
+#pragma unroll
+  for (int i = 0; i < NST; i++)
+    if ((uint32_t)i < nch) issue((uint32_t)i, i);
+  const uint32_t nb_total = (uint32_t)(len >> 6), r = (uint32_t)(len & 63u);
+  const uint32_t total = nb_total + (r < 56 ? 1u : 2u);  // data blocks + padding block(s)
+  const uint32_t swz = (uint32_t)(lane & 7);
+  const uint32_t lane_off = (uint32_t)lane * 128u;
+  int stage = 0;
+  uint32_t phase = 0, chunk = 0;
+  mbar_wait(s_bar, 0);
+  phase = 1u;
+  // loads block `blk` (data, or the tail block turned into padding) into w; steps to the next stage when blk is its first block
+  auto load = [&](uint32_t blk, uint32_t* w) {
+    uint32_t c = blk / BPC;
+    if (c > nch - 1u) c = nch - 1u;  // a second padding block may lie one block past the last chunk: nothing is read for it
+    if (c != chunk) {  // warp-uniform; every block of the old stage is in registers or done: give the stage back
+      __syncwarp();
+      fence_proxy_async_smem();
+      if (chunk + NST < nch) issue(chunk + NST, stage);
+      if (++stage == NST) stage = 0;
+      mbar_wait(s_bar + 8 * stage, (phase >> stage) & 1u);
+      phase ^= 1u << stage;
+      chunk = c;
+    }
+    const uint32_t bb_raw = blk - c * BPC;
+    const uint32_t bb = bb_raw < BPC ? bb_raw : 0u;
+    const uint32_t a = s_tiles + stage * G::STAGE_BYTES + lane_off + (bb >> 1) * G::TILE;
+    const uint32_t q0 = (bb & 1u) * 4u;
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+      uint4 v = lds128(a + (((q0 + q) ^ swz) << 4));
+      w[4 * q] = v.x; w[4 * q + 1] = v.y; w[4 * q + 2] = v.z; w[4 * q + 3] = v.w;
+    }
+    if (blk >= nb_total) pad_block<A>(w, blk - nb_total, r, len);
+    if (A::BE) {
+#pragma unroll
+      for (int i = 0; i < 16; i++) w[i] = bswap(w[i]);
+    }
+  };
+  uint32_t wa[16], wb[16];
+  load(0u, wa);
+#pragma unroll 1
+  for (uint32_t blk = 0; blk < total; blk += 2) {
+    if (blk + 1 < total) load(blk + 1, wb);
+    A::compress(h, wa, one);
+    if (blk + 1 < total) {
+      if (blk + 2 < total) load(blk + 2, wa);
+      A::compress(h, wb, one);
+    }
+  }
+}
+
 // ------------------------------------------------------- few, large messages: schedule off-loading
 // When a GPU has fewer message groups than SM sub-partitions, every chain runs alone and the batch takes
 // exactly one chain's latency, however many SMs idle.  A chain cannot be split, but its message schedule
@@ -583,6 +661,15 @@ template <>
 struct Assist<Sha256> {
   static constexpr int WPB = 64;  // schedule words per block, K already added
   // w: the 16 big-endian message words.  Writes W[t]+K[t], t = 0..63, as 16 x 16 bytes per lane.
+  // V = 0: every add an ALU-pipe IADD3 (11 ALU instructions per schedule word); V = 1: the adds are IMADs on the FMA
+  // pipe (8 ALU + 4 FMA).  A warp alone on its sub-partition issues an instruction every 2.3 clocks while it feeds one
+  // pipe and every 1.4 when it alternates between the two (tools/microbench/chain.cu), so the mix matters even
+  // though nothing else competes for either pipe.
+  // KH: the round constants of words t < KH are added here, the others by the chain warp (rounds<V, KH>).  Both warps
+  // are issue-bound, so the adds go wherever they even out the pair (measured per block, tools/microbench/chain.cu:
+  // 64 constants cost the helper 185 cycles and the chain warp 160).
+  static constexpr int KH = 64;   // all in the helper: chain 1,630 cycles per block, helper 1,320 + ~300 of staging
+  template <int V = 0, int KH_ = KH>
   __device__ static __forceinline__ void expand(uint32_t* w, uint32_t dst, uint32_t one) {
     constexpr uint32_t K[64] = {
         0x428a2f98, 0x71374491, 0xb5c0fbcf, 0xe9b5dba5, 0x3956c25b, 0x59f111f1, 0x923f82a4, 0xab1c5ed5,
@@ -600,18 +687,34 @@ struct Assist<Sha256> {
         uint32_t x = w[(t - 15) & 15], y = w[(t - 2) & 15];
         uint32_t s0 = lop3<LUT_XOR3>(rotr(x, 7), rotr(x, 18), x >> 3);
         uint32_t s1 = lop3<LUT_XOR3>(rotr(y, 17), rotr(y, 19), y >> 10);
-        w[t & 15] = w[t & 15] + s0 + w[(t - 7) & 15] + s1;
+        if (V == 0) w[t & 15] = w[t & 15] + s0 + w[(t - 7) & 15] + s1;
+        else w[t & 15] = add_fma(add_fma(w[t & 15], w[(t - 7) & 15], one), add_fma(s0, s1, one), one);
       }
-      o[t & 3] = w[t & 15] + K[t];
+      o[t & 3] = t >= KH_ ? w[t & 15] : V == 0 ? w[t & 15] + K[t] : add_fma(w[t & 15], K[t], one);
       if ((t & 3) == 3) sts128(dst + (t >> 2) * 512, o[0], o[1], o[2], o[3]);
     }
-    (void)one;
   }
   // The 64 rounds of one block on pre-expanded W+K read from `src` (this lane's 16-byte column).
-  // A warp alone on its sub-partition issues about one instruction every two clocks whatever the pipe, so both
-  // the instruction count and the e -> S1 -> e dependence matter: the 14-instruction form (en = d + t1) measured
-  // 262 ms per 16 MiB part, this 15-instruction form with en computed beside t1 247 ms.
+  // The chain warp runs alone on its sub-partition, so its speed is its own issue rate: an instruction every ~2.3
+  // clocks per pipe, ~1.4 when consecutive instructions alternate between the ALU and the FMA pipe (measured,
+  // tools/microbench/chain.cu).  The rotates and booleans (10 per round) can only run on the ALU pipe; the variants
+  // differ in where the round's adds go:
+  //   V = 0  13 ALU + 2 FMA: three IADD3 (t1, e', a'), hh + wk and d + hh + wk as IMADs         (round 1: 29 clk/round)
+  //   V = 1  11 ALU + 6 FMA: t1 and e' as IMAD pairs, a' = IADD3(t1, S0, maj)
+  //   V = 2  10 ALU + 8 FMA: a' as an IMAD pair as well
+  //   V = 3  10 ALU + 6 FMA: e' = d + t1 (one IMAD after t1, no separate d + hh + wk), a' as an IMAD pair
+  //   V = 4  11 ALU + 4 FMA: as 3 but a' = IADD3
+  template <int V = 1, int KH_ = KH>
   __device__ static __forceinline__ void rounds(uint32_t* h, const uint4* src, uint32_t one) {
+    constexpr uint32_t K[64] = {
+        0x428a2f98, 0x71374491, 0xb5c0fbcf, 0xe9b5dba5, 0x3956c25b, 0x59f111f1, 0x923f82a4, 0xab1c5ed5,
+        0xd807aa98, 0x12835b01, 0x243185be, 0x550c7dc3, 0x72be5d74, 0x80deb1fe, 0x9bdc06a7, 0xc19bf174,
+        0xe49b69c1, 0xefbe4786, 0x0fc19dc6, 0x240ca1cc, 0x2de92c6f, 0x4a7484aa, 0x5cb0a9dc, 0x76f988da,
+        0x983e5152, 0xa831c66d, 0xb00327c8, 0xbf597fc7, 0xc6e00bf3, 0xd5a79147, 0x06ca6351, 0x14292967,
+        0x27b70a85, 0x2e1b2138, 0x4d2c6dfc, 0x53380d13, 0x650a7354, 0x766a0abb, 0x81c2c92e, 0x92722c85,
+        0xa2bfe8a1, 0xa81a664b, 0xc24b8b70, 0xc76c51a3, 0xd192e819, 0xd6990624, 0xf40e3585, 0x106aa070,
+        0x19a4c116, 0x1e376c08, 0x2748774c, 0x34b0bcb5, 0x391c0cb3, 0x4ed8aa4a, 0x5b9cca4f, 0x682e6ff3,
+        0x748f82ee, 0x78a5636f, 0x84c87814, 0x8cc70208, 0x90befffa, 0xa4506ceb, 0xbef9a3f7, 0xc67178f2};
     uint32_t a = h[0], b = h[1], c = h[2], d = h[3], e = h[4], f = h[5], g = h[6], hh = h[7];
 #pragma unroll
     for (int q = 0; q < 16; q++) {
@@ -619,26 +722,100 @@ struct Assist<Sha256> {
       const uint32_t wk[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
       for (int j = 0; j < 4; j++) {
-        uint32_t S1 = lop3<LUT_XOR3>(rotr(e, 6), rotr(e, 11), rotr(e, 25));
-        // hh + wk and d + hh + wk do not depend on this round's inputs: two IMADs off the critical path;
-        // the three adds that do are IADD3s (13 ALU + 2 FMA instructions per round)
-        const uint32_t p = add_fma(hh, wk[j], one);
-        const uint32_t dp = add_fma(d, p, one);
+        const uint32_t S1 = lop3<LUT_XOR3>(rotr(e, 6), rotr(e, 11), rotr(e, 25));
         const uint32_t ch = lop3<LUT_CH>(e, f, g);
-        const uint32_t t1 = p + ch + S1;
-        const uint32_t en = dp + ch + S1;
-        uint32_t S0 = lop3<LUT_XOR3>(rotr(a, 2), rotr(a, 13), rotr(a, 22));
-        uint32_t mj = lop3<LUT_MAJ>(a, b, c);
-        hh = g; g = f; f = e; e = en; d = c; c = b; b = a; a = t1 + S0 + mj;
+        const uint32_t S0 = lop3<LUT_XOR3>(rotr(a, 2), rotr(a, 13), rotr(a, 22));
+        const uint32_t mj = lop3<LUT_MAJ>(a, b, c);
+        // hh + K[t] + w: nothing of this round's inputs; from word KH on the constant is added here (hh is four rounds old)
+        const uint32_t p = 4 * q + j >= KH_ ? add_fma(add_fma(hh, K[4 * q + j], one), wk[j], one) : add_fma(hh, wk[j], one);
+        uint32_t t1, en, an;
+        if (V == 0) {
+          const uint32_t dp = add_fma(d, p, one);
+          t1 = p + ch + S1;
+          en = dp + ch + S1;
+          an = t1 + S0 + mj;
+        } else if (V == 1 || V == 2) {
+          const uint32_t dp = add_fma(d, p, one);
+          t1 = add_fma(add_fma(p, ch, one), S1, one);
+          en = add_fma(add_fma(dp, ch, one), S1, one);
+          an = V == 1 ? t1 + S0 + mj : add_fma(t1, add_fma(S0, mj, one), one);
+        } else {
+          t1 = add_fma(add_fma(p, ch, one), S1, one);
+          en = add_fma(d, t1, one);
+          an = V == 4 ? t1 + S0 + mj : add_fma(t1, add_fma(S0, mj, one), one);
+        }
+        hh = g; g = f; f = e; e = en; d = c; c = b; b = a; a = an;
       }
     }
     h[0] += a; h[1] += b; h[2] += c; h[3] += d; h[4] += e; h[5] += f; h[6] += g; h[7] += hh;
   }
 };
 
+// One MD5 step with a run-time-looking index that is a constant after full unrolling (the fused helper below
+// interleaves MD5 step t with schedule word t in SOURCE order; ptxas keeps that order where latencies allow).
+// s[0..3] = a, b, c, d of RFC 1321; step t rotates the roles: its "a" is s[(4 - t) & 3].
+__device__ __forceinline__ void md5_step_at(uint32_t* s, const uint32_t* m, int t, uint32_t one) {
+  constexpr uint32_t T[64] = {
+      0xd76aa478, 0xe8c7b756, 0x242070db, 0xc1bdceee, 0xf57c0faf, 0x4787c62a, 0xa8304613, 0xfd469501,
+      0x698098d8, 0x8b44f7af, 0xffff5bb1, 0x895cd7be, 0x6b901122, 0xfd987193, 0xa679438e, 0x49b40821,
+      0xf61e2562, 0xc040b340, 0x265e5a51, 0xe9b6c7aa, 0xd62f105d, 0x02441453, 0xd8a1e681, 0xe7d3fbc8,
+      0x21e1cde6, 0xc33707d6, 0xf4d50d87, 0x455a14ed, 0xa9e3e905, 0xfcefa3f8, 0x676f02d9, 0x8d2a4c8a,
+      0xfffa3942, 0x8771f681, 0x6d9d6122, 0xfde5380c, 0xa4beea44, 0x4bdecfa9, 0xf6bb4b60, 0xbebfbc70,
+      0x289b7ec6, 0xeaa127fa, 0xd4ef3085, 0x04881d05, 0xd9d4d039, 0xe6db99e5, 0x1fa27cf8, 0xc4ac5665,
+      0xf4292244, 0x432aff97, 0xab9423a7, 0xfc93a039, 0x655b59c3, 0x8f0ccc92, 0xffeff47d, 0x85845dd1,
+      0x6fa87e4f, 0xfe2ce6e0, 0xa3014314, 0x4e0811a1, 0xf7537e82, 0xbd3af235, 0x2ad7d2bb, 0xeb86d391};
+  constexpr int S[16] = {7, 12, 17, 22, 5, 9, 14, 20, 4, 11, 16, 23, 6, 10, 15, 21};
+  const int r = t >> 4;
+  const int g = r == 0 ? t : r == 1 ? (5 * t + 1) & 15 : r == 2 ? (3 * t + 5) & 15 : (7 * t) & 15;
+  uint32_t& a = s[(4 - t) & 3];
+  const uint32_t b = s[(5 - t) & 3], c = s[(6 - t) & 3], d = s[(7 - t) & 3];
+  const uint32_t f = r == 0 ? lop3<LUT_CH>(b, c, d) : r == 1 ? lop3<LUT_CH>(d, b, c)
+                   : r == 2 ? lop3<LUT_XOR3>(b, c, d) : lop3<LUT_MD5I>(b, c, d);
+  const uint32_t akm = a + add_fma(m[g], T[t], one);
+  a = b + rotl(akm + f, S[(r << 2) | (t & 3)]);
+}
+
+// Helper body of the fused MD5 + SHA-256 kernel: SHA-256 schedule word t (as Assist<Sha256>::expand<V>) and MD5 step t,
+// alternately, t = 0..63.  w: 16 big-endian words (rolling window, destroyed); m: the same block as 16 little-endian
+// words with MD5's padding; hm: MD5 chaining value.
+template <int V = 0, int KH_ = Assist<Sha256>::KH>
+__device__ __forceinline__ void expand_sha256_with_md5(uint32_t* w, const uint32_t* m, uint32_t* hm, uint32_t dst, uint32_t one) {
+  constexpr uint32_t K[64] = {
+      0x428a2f98, 0x71374491, 0xb5c0fbcf, 0xe9b5dba5, 0x3956c25b, 0x59f111f1, 0x923f82a4, 0xab1c5ed5,
+      0xd807aa98, 0x12835b01, 0x243185be, 0x550c7dc3, 0x72be5d74, 0x80deb1fe, 0x9bdc06a7, 0xc19bf174,
+      0xe49b69c1, 0xefbe4786, 0x0fc19dc6, 0x240ca1cc, 0x2de92c6f, 0x4a7484aa, 0x5cb0a9dc, 0x76f988da,
+      0x983e5152, 0xa831c66d, 0xb00327c8, 0xbf597fc7, 0xc6e00bf3, 0xd5a79147, 0x06ca6351, 0x14292967,
+      0x27b70a85, 0x2e1b2138, 0x4d2c6dfc, 0x53380d13, 0x650a7354, 0x766a0abb, 0x81c2c92e, 0x92722c85,
+      0xa2bfe8a1, 0xa81a664b, 0xc24b8b70, 0xc76c51a3, 0xd192e819, 0xd6990624, 0xf40e3585, 0x106aa070,
+      0x19a4c116, 0x1e376c08, 0x2748774c, 0x34b0bcb5, 0x391c0cb3, 0x4ed8aa4a, 0x5b9cca4f, 0x682e6ff3,
+      0x748f82ee, 0x78a5636f, 0x84c87814, 0x8cc70208, 0x90befffa, 0xa4506ceb, 0xbef9a3f7, 0xc67178f2};
+  uint32_t s[4] = {hm[0], hm[1], hm[2], hm[3]};
+  uint32_t o[4];
+#pragma unroll
+  for (int t = 0; t < 64; t++) {
+    if (t >= 16) {
+      uint32_t x = w[(t - 15) & 15], y = w[(t - 2) & 15];
+      uint32_t s0 = lop3<LUT_XOR3>(rotr(x, 7), rotr(x, 18), x >> 3);
+      uint32_t s1 = lop3<LUT_XOR3>(rotr(y, 17), rotr(y, 19), y >> 10);
+      if (V == 0) w[t & 15] = w[t & 15] + s0 + w[(t - 7) & 15] + s1;
+      else w[t & 15] = add_fma(add_fma(w[t & 15], w[(t - 7) & 15], one), add_fma(s0, s1, one), one);
+    }
+    o[t & 3] = t >= KH_ ? w[t & 15] : V == 0 ? w[t & 15] + K[t] : add_fma(w[t & 15], K[t], one);
+    md5_step_at(s, m, t, one);
+    if ((t & 3) == 3) sts128(dst + (t >> 2) * 512, o[0], o[1], o[2], o[3]);
+  }
+  hm[0] += s[0]; hm[1] += s[1]; hm[2] += s[2]; hm[3] += s[3];
+}
+
 template <>
 struct Assist<Sha1> {
   static constexpr int WPB = 80;
+  // KH: the round constants of words t < KH are added here, the others by the chain warp (rounds<V, KH>).  Per block the
+  // 80 constants cost the helper 219 cycles and the chain warp 62 (tools/microbench/chain.cu); with all of them in
+  // the helper the pair ran at the helper's pace (ncu: the chain warp waited at the hand-over barrier), with all of
+  // them in the chain warp at the chain's — the split evens the two out.
+  static constexpr int KH = 80;   // all in the helper (a 32 / 48 split measured 2 % slower in the kernel than either end)
+  template <int KH_ = KH>
   __device__ static __forceinline__ void expand(uint32_t* w, uint32_t dst, uint32_t one) {
     uint32_t o[4];
 #pragma unroll
@@ -646,13 +823,15 @@ struct Assist<Sha1> {
       if (t >= 16)
         w[t & 15] = rotl(lop3<LUT_XOR3>(w[(t - 3) & 15], w[(t - 8) & 15], w[(t - 14) & 15]) ^ w[t & 15], 1);
       const uint32_t k = t < 20 ? 0x5a827999u : t < 40 ? 0x6ed9eba1u : t < 60 ? 0x8f1bbcdcu : 0xca62c1d6u;
-      o[t & 3] = add_fma(w[t & 15], k, one);  // + K on the FMA pipe (the helper's other work is all ALU; measured neutral)
+      o[t & 3] = t >= KH_ ? w[t & 15] : add_fma(w[t & 15], k, one);
       if ((t & 3) == 3) sts128(dst + (t >> 2) * 512, o[0], o[1], o[2], o[3]);
     }
   }
+  // V = 0: x = IADD3(e, wk, f) — 4 ALU instructions per round; V = 1: x = (e + wk) + f as two IMADs — 3 ALU + 2 FMA
+  // (e + wk is off the chain; the second IMAD is on it).  See Assist<Sha256>::rounds for why the mix matters.
+  template <int V = 0, int KH_ = KH>
   __device__ static __forceinline__ void rounds(uint32_t* h, const uint4* src, uint32_t one) {
     uint32_t a = h[0], b = h[1], c = h[2], d = h[3], e = h[4];
-    (void)one;
 #pragma unroll
     for (int q = 0; q < 20; q++) {
       const uint4 v = src[q * 32];
@@ -662,7 +841,9 @@ struct Assist<Sha1> {
         const int t = 4 * q + j;
         uint32_t f = t < 20 ? lop3<LUT_CH>(b, c, d) : t < 40 ? lop3<LUT_XOR3>(b, c, d)
                    : t < 60 ? lop3<LUT_MAJ>(b, c, d) : lop3<LUT_XOR3>(b, c, d);
-        uint32_t x = e + wk[j] + f;
+        const uint32_t k = t < 20 ? 0x5a827999u : t < 40 ? 0x6ed9eba1u : t < 60 ? 0x8f1bbcdcu : 0xca62c1d6u;
+        const uint32_t ek = t >= KH_ ? add_fma(e, k, one) : e;  // e is four rounds old: an IMAD on the otherwise idle FMA pipe
+        uint32_t x = V == 0 ? ek + wk[j] + f : add_fma(add_fma(ek, wk[j], one), f, one);
         uint32_t tmp = rotl(a, 5) + x;
         e = d; d = c; c = rotl(b, 30); b = a; a = tmp;
       }
@@ -735,8 +916,8 @@ __device__ __forceinline__ void assist_produce(const void* tmap, uint32_t row0, 
 #pragma unroll
       for (int i = 0; i < 16; i++) w[i] = bswap(w[i]);
       if (produced >= (uint32_t)SS) nb_sync(1 + SS + slot);  // wait until the chain warp has drained this slot
-      if (MD5_TOO) Md5::compress(hm, m, one);                // one basic block with the expansion: ptxas interleaves them
-      Assist<A>::expand(w, s_ring + slot * SLOT + lane * 16, one);
+      if (MD5_TOO) expand_sha256_with_md5(w, m, hm, s_ring + slot * SLOT + lane * 16, one);  // schedule word t / MD5 step t, alternately
+      else Assist<A>::expand(w, s_ring + slot * SLOT + lane * 16, one);
       nb_arrive(1 + slot);
       produced++;
       if (++slot == SS) slot = 0;

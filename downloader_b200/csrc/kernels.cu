@@ -106,6 +106,7 @@ struct TileArgs {
   uint32_t* ok_bits;        // SHA-1 only, nullable
   uint32_t one;             // the value 1, opaque to the compiler (see add_fma)
   uint32_t salt;            // small grids: CTA b works on group (b + gridDim.x - salt) % gridDim.x, see spread_group
+  uint32_t lone;            // tile kernel: at most ~one warp per sub-partition (the prefetching stream pays off)
 };
 
 // A kernel with only a few CTAs always gets the same first SMs, so several such kernels running at once
@@ -163,8 +164,12 @@ __global__ void __launch_bounds__(32) digest_tile_kernel(const __grid_constant__
   const uint32_t nch = (uint32_t)(p.len / G::CH) + 1u;
   uint32_t h[A::NS];
   A::init(h);
-  PipeState ps;
-  tile_segment<A, K, NST>(&tmap, group * 32u, p.len, 0u, nch, nch, h, s_tiles, s_bar, lane, ps, p.one);
+  if (A::DLEN == 16 && p.lone) {  // MD5 chains with a sub-partition to themselves: latency-bound, see tile_stream_prefetch
+    tile_stream_prefetch<A, K, NST>(&tmap, group * 32u, p.len, nch, h, s_tiles, s_bar, lane, p.one);
+  } else {
+    PipeState ps;
+    tile_segment<A, K, NST>(&tmap, group * 32u, p.len, 0u, nch, nch, h, s_tiles, s_bar, lane, ps, p.one);
+  }
   finish_group<A>(p, group, lane, h);
 }
 
@@ -453,7 +458,8 @@ struct TileOpts {
   int sliced_min_groups = 592;  // auto: use the sliced kernel from this many 32-message groups
   int tile_many_groups = 8192;  // auto: SHA-1 / SHA-256 batches with at least this many groups go back to one-warp CTAs
                                 // (many waves balance themselves and measured 1-12 % faster than the persistent kernel)
-  int fuse_md5_sha256 = 1;      // th_md5_sha256_batch: 1 = one chain + helper kernel does both where the plan is "assist"
+  int md5_prefetch = 0;         // MD5 tile kernel with <= 4 groups per SM: load block b+1 before compressing block b
+  int fuse_md5_sha256 = 0;      // th_md5_sha256_batch: 1 = one chain + helper kernel does both where the plan is "assist" (measured slower: DESIGN.md §7)
   int ragged_rows = 1;          // per-lane kernels: 1 = cooperative cp.async row tiles, 0 = one bulk copy per lane
   int rows_variant[3] = {2, 2, 2};  // index into g_rows_variants per digest
 };
@@ -579,13 +585,14 @@ static int launch_uniform(int ai, const void* d_base, uint64_t stride, uint64_t 
   if (d_out_md5 && (pl.path != 4 || ai != 2)) return 1;
   CUtensorMap tmap;
   if (!make_tmap(&tmap, d_base, len, stride, n)) return 1;
-  TileArgs a{len, n, pl.segc, pl.nseg, d_out, d_out_md5, d_expected, d_ok_bits, 1u, 0u};
+  TileArgs a{len, n, pl.segc, pl.nseg, d_out, d_out_md5, d_expected, d_ok_bits, 1u, 0u, 0u};
   uint32_t grid = pl.grid;
   size_t pad = 0;
   if (pl.path != 3) {  // few CTAs: pad to one per SM and rotate by a per-launch salt (see spread_group)
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    a.lone = (pl.path == 2 && grid <= 4u * (uint32_t)sms && g_opts.md5_prefetch) ? 1u : 0u;
     if (grid <= (uint32_t)sms) {
       static std::atomic<uint32_t> launches{0};
       a.salt = (launches.fetch_add(1) * 37u) % (uint32_t)sms;
@@ -829,6 +836,7 @@ int th_set_option(const char* name, long long value) {
   if (k == "tile_many_groups") { if (value < 1) return TH_EINVAL; th::g_opts.tile_many_groups = (int)value; return TH_OK; }
   if (k == "sliced_min_groups") { if (value < 1) return TH_EINVAL; th::g_opts.sliced_min_groups = (int)value; return TH_OK; }
   if (k == "ragged_rows") { if (value < 0 || value > 1) return TH_EINVAL; th::g_opts.ragged_rows = (int)value; return TH_OK; }
+  if (k == "md5_prefetch") { if (value < 0 || value > 1) return TH_EINVAL; th::g_opts.md5_prefetch = (int)value; return TH_OK; }
   if (k == "fuse_md5_sha256") { if (value < 0 || value > 1) return TH_EINVAL; th::g_opts.fuse_md5_sha256 = (int)value; return TH_OK; }
   if (k == "rows_variant") {
     if (value < 0 || value >= th::kNumRowsVariants) return TH_EINVAL;

@@ -216,36 +216,36 @@ def test_assist_kernel_schedule_offload(torch, L):
 
 @pytest.mark.parametrize("n,ln", [(1, 1024), (5, 4096 + 55), (33, 100000 + 56), (64, (1 << 20) + 63), (40, 262144), (3, 1 << 20), (7, 16 << 20)])
 def test_fused_md5_sha256_kernel_vs_hashlib(torch, L, n, ln):
-    """MD5 + SHA-256 of few large equal-length messages in ONE launch: the SHA-256 chain's helper warp runs the MD5
-    chain on the words it holds (kernels.cu, MD5_TOO).  Tail lengths cover one and two padding blocks, where MD5 and
-    SHA-256 pad differently (little- vs big-endian bit length); rows past n are zero-filled by the TMA unit."""
+    """th_set_option("fuse_md5_sha256", 1): MD5 + SHA-256 of few large equal-length messages in ONE launch — the SHA-256
+    chain's helper warp runs the MD5 chain on the words it holds (kernels.cu, MD5_TOO).  Off by default (it measured
+    slower than the two concurrent kernels) but kept selectable, so it is kept correct.  Tail lengths
+    cover one and two padding blocks, where MD5 and SHA-256 pad differently (little- vs big-endian bit length)."""
     stride = (ln + 15) & ~15
     rng = np.random.default_rng(n * 7919 + ln)
     host = rng.integers(0, 256, n * stride, dtype=np.uint8)
     d = torch.from_numpy(host).cuda()
-    assert L.th_md5_sha256_fused(stride, ln, n) == 1
-    o5 = torch.full((n * 16,), 0xEE, dtype=torch.uint8, device="cuda")
-    o256 = torch.full((n * 32,), 0xEE, dtype=torch.uint8, device="cuda")
-    assert L.th_md5_sha256_batch(d.data_ptr(), stride, ln, n, o5.data_ptr(), o256.data_ptr(), None) == 0
-    torch.cuda.synchronize()
     bufs = [host[i * stride:i * stride + ln] for i in range(n)]
-    assert (o5.cpu().numpy().reshape(n, 16) == ref_digests(MD5, bufs)).all()
-    assert (o256.cpu().numpy().reshape(n, 32) == ref_digests(SHA256, bufs)).all()
-    # switched off: the same call runs the two separate kernels and gives the same bytes
-    assert L.th_set_option(b"fuse_md5_sha256", 0) == 0
+    assert L.th_md5_sha256_fused(stride, ln, n) == 0  # the default: two launches, one after the other on the stream
+    p5 = torch.full((n * 16,), 0xEE, dtype=torch.uint8, device="cuda")
+    p256 = torch.full((n * 32,), 0xEE, dtype=torch.uint8, device="cuda")
+    assert L.th_md5_sha256_batch(d.data_ptr(), stride, ln, n, p5.data_ptr(), p256.data_ptr(), None) == 0
+    torch.cuda.synchronize()
+    assert (p5.cpu().numpy().reshape(n, 16) == ref_digests(MD5, bufs)).all()
+    assert (p256.cpu().numpy().reshape(n, 32) == ref_digests(SHA256, bufs)).all()
+    assert L.th_set_option(b"fuse_md5_sha256", 1) == 0
     try:
-        assert L.th_md5_sha256_fused(stride, ln, n) == 0
-        p5, p256 = torch.zeros_like(o5), torch.zeros_like(o256)
-        assert L.th_md5_sha256_batch(d.data_ptr(), stride, ln, n, p5.data_ptr(), p256.data_ptr(), None) == 0
+        assert L.th_md5_sha256_fused(stride, ln, n) == 1
+        o5, o256 = torch.zeros_like(p5), torch.zeros_like(p256)
+        assert L.th_md5_sha256_batch(d.data_ptr(), stride, ln, n, o5.data_ptr(), o256.data_ptr(), None) == 0
         torch.cuda.synchronize()
         assert torch.equal(p5, o5) and torch.equal(p256, o256)
     finally:
-        assert L.th_set_option(b"fuse_md5_sha256", 1) == 0
+        assert L.th_set_option(b"fuse_md5_sha256", 0) == 0
 
 
-def test_submit_md5_and_sha256_of_parts_share_one_launch(torch):
-    """th_submit with MD5 | SHA-256 over an object's parts (equal-length prefix + short last part): each launch item
-    is one fused kernel, so 2 launches instead of 4; SHA-1 of the same slot still has its own."""
+def test_submit_md5_and_sha256_of_parts_can_share_one_launch(torch, L):
+    """With the fused kernel switched on, th_submit with MD5 | SHA-256 over an object's parts (equal-length prefix +
+    short last part) launches one kernel per item — 2 instead of 4; SHA-1 of the same slot still has its own."""
     from downloader_b200 import Engine
     part, last = 4 << 20, (1 << 20) + 12345
     nparts = 6
@@ -254,25 +254,36 @@ def test_submit_md5_and_sha256_of_parts_share_one_launch(torch):
     data = rng.integers(0, 256, total, dtype=np.uint8)
     offs = np.arange(nparts, dtype=np.uint64) * part
     lens = np.array([part] * (nparts - 1) + [last], np.uint64)
-    with Engine([0], ring_bytes=64 << 20) as e:
-        e.set_timing(True)
+    bufs = [data[int(o):int(o + l)] for o, l in zip(offs, lens)]
+    assert L.th_set_option(b"fuse_md5_sha256", 1) == 0
+    try:
+        with Engine([0], ring_bytes=64 << 20) as e:
+            e.set_timing(True)
+            slot, view = e.ring_acquire(total)
+            view[:] = data
+            s0 = e.stats()
+            t = e.submit(slot, offs, lens, MD5 | SHA256)
+            tm = e.timing(t)
+            r = e.result(t, nparts, MD5 | SHA256)
+            s1 = e.stats()
+            assert (r[MD5] == ref_digests(MD5, bufs)).all() and (r[SHA256] == ref_digests(SHA256, bufs)).all()
+            assert s1["launches"] - s0["launches"] == 2
+            assert tm[3] >= 0 and tm[4] > tm[3] and tm[6] > tm[5]  # the MD5 timeline is the fused launches'
+            slot, view = e.ring_acquire(total)
+            view[:] = data
+            t = e.submit(slot, offs, lens, SHA1 | MD5 | SHA256)
+            r = e.result(t, nparts, SHA1 | MD5 | SHA256)
+            assert (r[SHA1] == ref_digests(SHA1, bufs)).all() and (r[MD5] == ref_digests(MD5, bufs)).all()
+            assert e.stats()["launches"] - s1["launches"] == 4
+    finally:
+        assert L.th_set_option(b"fuse_md5_sha256", 0) == 0
+    with Engine([0], ring_bytes=64 << 20) as e:  # the default: separate MD5 and SHA-256 kernels on separate streams
         slot, view = e.ring_acquire(total)
         view[:] = data
         s0 = e.stats()
-        t = e.submit(slot, offs, lens, MD5 | SHA256)
-        tm = e.timing(t)
-        r = e.result(t, nparts, MD5 | SHA256)
-        s1 = e.stats()
-        bufs = [data[int(o):int(o + l)] for o, l in zip(offs, lens)]
+        r = e.result(e.submit(slot, offs, lens, MD5 | SHA256), nparts, MD5 | SHA256)
         assert (r[MD5] == ref_digests(MD5, bufs)).all() and (r[SHA256] == ref_digests(SHA256, bufs)).all()
-        assert s1["launches"] - s0["launches"] == 2
-        assert tm[3] >= 0 and tm[4] > tm[3] and tm[6] > tm[5]  # the MD5 timeline is the fused launches'
-        slot, view = e.ring_acquire(total)
-        view[:] = data
-        t = e.submit(slot, offs, lens, SHA1 | MD5 | SHA256)
-        r = e.result(t, nparts, SHA1 | MD5 | SHA256)
-        assert (r[SHA1] == ref_digests(SHA1, bufs)).all() and (r[MD5] == ref_digests(MD5, bufs)).all()
-        assert e.stats()["launches"] - s1["launches"] == 4
+        assert e.stats()["launches"] - s0["launches"] == 4
 
 
 def test_sliced_kernel_time_slicing_engaged(torch, L):
@@ -586,7 +597,7 @@ def test_few_large_ragged_messages_take_lone_launches(eng):
     s1 = eng.stats()
     for a in (SHA1, MD5, SHA256):
         assert (out[a] == ref_digests(a, bufs)).all(), NAMES[a]
-    assert s1["launches"] - s0["launches"] == 2 * len(lens)  # per message: SHA-1, and one fused MD5 + SHA-256 launch
+    assert s1["launches"] - s0["launches"] == 3 * len(lens)  # one launch per message and digest
     exp = ref_digests(SHA1, bufs).copy()
     exp[2, 0] ^= 1
     out = eng.hash_batch(bufs, SHA1 | MD5, expected_sha1=exp)
@@ -751,7 +762,7 @@ def test_heavy_tailed_batch_peels_outliers_into_lone_launches(eng):
     for a in (SHA1, MD5, SHA256):
         wrong = np.nonzero((out[a] != ref_digests(a, bufs)).any(axis=1))[0]
         assert wrong.size == 0, (NAMES[a], [lens[i] for i in wrong[:5]])
-    assert s1["launches"] - s0["launches"] == 3 + 2 * len(big)  # per-lane remainder x 3 digests; outliers: SHA-1 + fused MD5/SHA-256
+    assert s1["launches"] - s0["launches"] == 3 * (1 + len(big))
     # with a verify table the remainder stays one launch (the bitfield word is written by one ballot)
     exp = ref_digests(SHA1, bufs).copy()
     exp[40, 3] ^= 0x10

@@ -69,8 +69,10 @@ __global__ void md5_step_k(uint32_t* out, uint32_t one, uint32_t seed, long long
   (void)one;
 }
 
-// MODE 0 md5 compress, 1 sha1 compress, 2 sha256 compress (message words in registers, made opaque every block),
-// 3 sha1 chain-warp rounds, 4 sha256 chain-warp rounds (pre-expanded W+K read from shared memory with LDS.128)
+// MODE 0 md5 compress, 1 sha1 compress, 2 sha256 compress (message words in registers, made opaque every block);
+// 10+V sha1 chain-warp rounds variant V, 20+V sha256 chain-warp rounds variant V (pre-expanded W+K read from shared
+// memory with LDS.128); 30 sha1 helper expansion, 40+V sha256 helper expansion variant V (written to shared memory),
+// 50+V the same with the MD5 chain of the block interleaved (the fused MD5 + SHA-256 helper)
 template <int MODE>
 __global__ void compress_k(uint32_t* out, uint32_t one, uint32_t seed, long long* cyc) {
   __shared__ uint4 ring[80 * 32];
@@ -82,24 +84,46 @@ __global__ void compress_k(uint32_t* out, uint32_t one, uint32_t seed, long long
   for (int i = 0; i < 8; i++) h[i] = seed * (i + 1) + lane;
 #pragma unroll
   for (int i = 0; i < 16; i++) w[i] = seed * (i + 11) ^ lane;
+  const uint32_t dst = smem_u32(ring) + lane * 16;
   const long long t0 = clock64();
 #pragma unroll 1
   for (int it = 0; it < NBLK; it++) {
-    if (MODE <= 2) {
+    if (MODE <= 2 || MODE >= 30) {
 #pragma unroll
       for (int i = 0; i < 16; i++) opaque(w[i]);
     }
     if (MODE == 0) Md5::compress(h, w, one);
     if (MODE == 1) { uint32_t v[16]; for (int i = 0; i < 16; i++) v[i] = w[i]; Sha1::compress(h, v, one); }
     if (MODE == 2) { uint32_t v[16]; for (int i = 0; i < 16; i++) v[i] = w[i]; Sha256::compress(h, v, one); }
-    if (MODE == 3) Assist<Sha1>::rounds(h, ring + lane, one);
-    if (MODE == 4) Assist<Sha256>::rounds(h, ring + lane, one);
+    if (MODE >= 10 && MODE < 20) Assist<Sha1>::rounds<MODE - 10, 80>(h, ring + lane, one);
+    if (MODE >= 20 && MODE < 30) Assist<Sha256>::rounds<MODE - 20, 64>(h, ring + lane, one);
+    if (MODE >= 110 && MODE < 120) Assist<Sha1>::rounds<MODE - 110, 0>(h, ring + lane, one);   // + K in the chain warp
+    if (MODE >= 120 && MODE < 130) Assist<Sha256>::rounds<MODE - 120, 0>(h, ring + lane, one);
+    // (the expanded window is fed back into w[0]: without a loop-carried value the compiler hoists the whole expansion)
+    if (MODE == 30) { uint32_t v[16]; for (int i = 0; i < 16; i++) v[i] = bswap(w[i]); Assist<Sha1>::expand<80>(v, dst, one); w[0] += v[15]; }
+    if (MODE == 130) { uint32_t v[16]; for (int i = 0; i < 16; i++) v[i] = bswap(w[i]); Assist<Sha1>::expand<0>(v, dst, one); w[0] += v[15]; }
+    if (MODE >= 140 && MODE < 150) { uint32_t v[16]; for (int i = 0; i < 16; i++) v[i] = bswap(w[i]); Assist<Sha256>::expand<MODE - 140, 0>(v, dst, one); w[0] += v[15]; }
+    if (MODE >= 160 && MODE < 170) { uint32_t v[16]; for (int i = 0; i < 16; i++) v[i] = bswap(w[i]); expand_sha256_with_md5<MODE - 160, 0>(v, w, h, dst, one); w[0] += v[15]; }
+    if (MODE >= 40 && MODE < 50) { uint32_t v[16]; for (int i = 0; i < 16; i++) v[i] = bswap(w[i]); Assist<Sha256>::expand<MODE - 40, 64>(v, dst, one); w[0] += v[15]; }
+    if (MODE >= 50 && MODE < 60) {  // MD5 block, then the expansion, as two calls (ptxas is left to interleave them)
+      uint32_t v[16];
+      for (int i = 0; i < 16; i++) v[i] = bswap(w[i]);
+      Md5::compress(h, w, one);
+      Assist<Sha256>::expand<MODE - 50, 64>(v, dst, one);
+      w[0] += v[15];
+    }
+    if (MODE >= 60 && MODE < 70) {  // schedule word t / MD5 step t alternately in source order (what the kernel uses)
+      uint32_t v[16];
+      for (int i = 0; i < 16; i++) v[i] = bswap(w[i]);
+      expand_sha256_with_md5<MODE - 60, 64>(v, w, h, dst, one);
+      w[0] += v[15];
+    }
   }
   const long long t1 = clock64();
   uint32_t x = 0;
 #pragma unroll
   for (int i = 0; i < 8; i++) x ^= h[i];
-  out[blockIdx.x * blockDim.x + threadIdx.x] = x;
+  out[blockIdx.x * blockDim.x + threadIdx.x] = x ^ ring[lane].x;
   if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
 }
 
@@ -135,8 +159,25 @@ int main() {
     printf("Md5::compress               %.1f cycles per block (%.2f per step)\n", run(compress_k<0>, shapes[s]) / NBLK, run(compress_k<0>, shapes[s]) / NBLK / 64);
     printf("Sha1::compress              %.1f cycles per block\n", run(compress_k<1>, shapes[s]) / NBLK);
     printf("Sha256::compress            %.1f cycles per block\n", run(compress_k<2>, shapes[s]) / NBLK);
-    printf("Assist<Sha1>::rounds        %.1f cycles per block (chain warp, schedule from shared memory)\n", run(compress_k<3>, shapes[s]) / NBLK);
-    printf("Assist<Sha256>::rounds      %.1f cycles per block\n", run(compress_k<4>, shapes[s]) / NBLK);
+    printf("Assist<Sha1>::rounds<0>     %.1f cycles per block (chain warp, schedule from shared memory; x = IADD3)\n", run(compress_k<10>, shapes[s]) / NBLK);
+    printf("Assist<Sha1>::rounds<1>     %.1f (x = two IMADs)\n", run(compress_k<11>, shapes[s]) / NBLK);
+    printf("Assist<Sha256>::rounds<0>   %.1f cycles per block (13 ALU + 2 FMA per round)\n", run(compress_k<20>, shapes[s]) / NBLK);
+    printf("Assist<Sha256>::rounds<1>   %.1f (11 ALU + 6 FMA)\n", run(compress_k<21>, shapes[s]) / NBLK);
+    printf("Assist<Sha256>::rounds<2>   %.1f (10 ALU + 8 FMA)\n", run(compress_k<22>, shapes[s]) / NBLK);
+    printf("Assist<Sha256>::rounds<3>   %.1f (10 ALU + 6 FMA)\n", run(compress_k<23>, shapes[s]) / NBLK);
+    printf("Assist<Sha256>::rounds<4>   %.1f (11 ALU + 4 FMA)\n", run(compress_k<24>, shapes[s]) / NBLK);
+    printf("Assist<Sha1>::expand        %.1f cycles per block (helper warp)\n", run(compress_k<30>, shapes[s]) / NBLK);
+    printf("Assist<Sha256>::expand<0>   %.1f (adds on the ALU pipe)\n", run(compress_k<40>, shapes[s]) / NBLK);
+    printf("Assist<Sha256>::expand<1>   %.1f (adds as IMAD)\n", run(compress_k<41>, shapes[s]) / NBLK);
+    printf("expand<0> + Md5::compress   %.1f (the fused MD5 + SHA-256 helper)\n", run(compress_k<50>, shapes[s]) / NBLK);
+    printf("expand<1> + Md5::compress   %.1f\n", run(compress_k<51>, shapes[s]) / NBLK);
+    printf("expand_sha256_with_md5<0>   %.1f (interleaved in source order)\n", run(compress_k<60>, shapes[s]) / NBLK);
+    printf("expand_sha256_with_md5<1>   %.1f\n", run(compress_k<61>, shapes[s]) / NBLK);
+    printf("-- round constants added by the chain warp instead of the helper:\n");
+    printf("Assist<Sha1>::rounds<0,K>   %.1f   rounds<1,K> %.1f   expand<K> %.1f\n", run(compress_k<110>, shapes[s]) / NBLK, run(compress_k<111>, shapes[s]) / NBLK, run(compress_k<130>, shapes[s]) / NBLK);
+    printf("Assist<Sha256>::rounds<0,K> %.1f   <1,K> %.1f   <4,K> %.1f   expand<0,K> %.1f   expand<1,K> %.1f   with_md5<0,K> %.1f\n",
+           run(compress_k<120>, shapes[s]) / NBLK, run(compress_k<121>, shapes[s]) / NBLK, run(compress_k<124>, shapes[s]) / NBLK,
+           run(compress_k<140>, shapes[s]) / NBLK, run(compress_k<141>, shapes[s]) / NBLK, run(compress_k<160>, shapes[s]) / NBLK);
   }
   return 0;
 }
