@@ -599,7 +599,7 @@ def main():
                     help="device staging ring = this many pinned rings (0: 1 for pieces, 3 for 16 MiB parts, whose chains outlast the copy)")
     ap.add_argument("--staging", default="", help="override bulk staging geometry, e.g. 512x2 (tuning only)")
     ap.add_argument("--path", type=int, default=0, help="0 auto, 1 bulk, 2 tile, 3 sliced (tuning only)")
-    ap.add_argument("--device-order", default="", help="comma-separated CUDA devices, rank r uses entry r (default: LOCAL_RANK)")
+    ap.add_argument("--device-order", default="auto", help="comma-separated CUDA devices, rank r uses entry r; 'auto' interleaves the two halves of the device list, 'identity' is LOCAL_RANK")
     ap.add_argument("--single-process", action="store_true", help="drive --gpus N devices from ONE process and one th_ctx (no torchrun)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
@@ -615,8 +615,8 @@ def main():
     E = Env()
     E.torch = torch
     E.rank, E.world, local, E.dist = dist_setup()
-    order = [int(x) for x in args.device_order.split(",")] if args.device_order else None
-    E.local = order[local] if order else local
+    order, order_why = device_order(args.device_order, torch.cuda.device_count(), E.world)
+    E.local = order[local]
     torch.cuda.set_device(E.local)
     E.L = L = _capi.lib()
     if args.staging:
@@ -648,7 +648,7 @@ def main():
         "scaling": "strong" if args.strong else "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
         "config": {"workload": desc, "algs": algs, "messages_per_gpu": n, "message_bytes": ln, "l2": head["l2"],
                    "kernel": head["kernel"], "verified_vs_oracle": head["verified_vs_oracle"],
-                   "fused_compare": algs == "sha1", "devices": "rank r -> cuda:%s" % (args.device_order or "r")},
+                   "fused_compare": algs == "sha1", "devices": {"rank_to_cuda": order[:E.world], "why": order_why}},
         "roofline": head["roofline"], "clocks": head["clocks"], "gpu_launches": head["gpu_launches"],
     }
     if "e2e" in head:
@@ -804,6 +804,21 @@ def run_single_process(args):
                       "overflow_allocs": st["overflow_allocs"],
                       "timing": "host wall clock around the streamed steps, last step drained inside; digests checked in the warm-up pass"}))
     return 0
+
+
+def device_order(spec, count, world):
+    """Which CUDA device each local rank uses.  'auto': the two halves of the device list interleaved (0, n/2, 1, n/2+1,
+    ...).  On this pool's 8-GPU boxes GPUs 0-3 and 4-7 sit behind two host bridges that each deliver ~115 GB/s of
+    pinned->device copies however many of their GPUs copy (profiles/r2_h2d_probe_8gpu.jsonl: {0,1,2,3} 115 GB/s,
+    {0,1,4,5} 212 GB/s), so a 2- or 4-rank run that takes its GPUs from both halves has twice the end-to-end ceiling of
+    one that takes GPUs 0..N-1.  With every GPU in use the order makes no difference."""
+    if spec not in ("auto", "identity", ""):
+        return [int(x) for x in spec.split(",")], "given on the command line"
+    if spec == "auto" and count >= 4 and count % 2 == 0 and world <= count:
+        half = count // 2
+        order = [x for pair in zip(range(half), range(half, count)) for x in pair]
+        return order, "halves of the device list interleaved: GPUs 0..n/2-1 and n/2..n-1 share one host bridge each (profiles/r2_h2d_probe_8gpu.jsonl)"
+    return list(range(max(count, world))), "LOCAL_RANK"
 
 
 def _mem_available():

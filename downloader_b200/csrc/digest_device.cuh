@@ -562,20 +562,24 @@ __device__ __forceinline__ void tile_segment(const void* tmap, uint32_t row0, ui
   }
 }
 
-// The same stream for a warp that runs ALONE on its sub-partition (few large messages, MD5): a lone MD5 chain is
-// latency-bound — its step is a 3-deep dependent chain, 12.1 clocks, of which only 4 issue slots are used — so everything
-// else a block needs (four LDS.128, the swizzled addresses, the tail tests, and once per stage the barrier wait and the
-// next TMA issue) is free IF it sits in the same basic block as a compression and does not feed it.  tile_segment loads
-// a block and then compresses it, so all of that is serial: 968 clocks per block measured against 807 for the bare
-// compression (tools/microbench/chain.cu).  Here block b+1 is loaded into a second register set before block b is
-// compressed (two blocks per loop trip, ping-pong, no register moves); moving on to the next stage happens inside that
-// prefetch, i.e. one block early, which also hands the stage back to the TMA unit one block sooner.
+// The same stream for a warp that runs ALONE on its sub-partition (few large messages, MD5).  A lone MD5 chain is
+// latency-bound: its step is a 3-deep dependent chain, 12.1 clocks, of which only 4 issue slots are used — so everything
+// else a block needs (four LDS.128 and their swizzled addresses) is free IF it sits in the same basic block as a
+// compression and does not feed it.  tile_segment loads a block, tests it for the tail, then compresses it: three
+// basic blocks, all serial — 968 clocks per block measured against 807 for the bare compression
+// (tools/microbench/chain.cu; ncu: 62 % of the samples are fixed-latency waits, 32 % issue).  Here the whole chunks of
+// the message run through a loop with no branch in it but its own back edge: per trip two compressions, each with the
+// loads of the block after next in front of it (two register sets, ping-pong, no moves).  The load that runs ahead
+// crosses into the next stage at the end of a chunk, so that stage's barrier is waited for at the START of the chunk
+// — which is why this wants NST >= 3: with two stages that chunk would only just have been requested.  The last,
+// partial chunk with its padding block(s) goes through the general loop.
 template <class A, int K, int NST>
-__device__ __forceinline__ void tile_stream_prefetch(const void* tmap, uint32_t row0, uint64_t len, uint32_t nch, uint32_t* h,
-                                                     uint32_t s_tiles, uint32_t s_bar, int lane, uint32_t one) {
+__device__ __forceinline__ void tile_stream_lone(const void* tmap, uint32_t row0, uint64_t len, uint32_t nch, uint32_t* h,
+                                                 uint32_t s_tiles, uint32_t s_bar, int lane, uint32_t one) {
+  static_assert(NST >= 3, "the run-ahead load needs the next stage to have been requested a whole chunk earlier");
   using G = Tiles<K, NST>;
   constexpr int CH = G::CH;
-  constexpr uint32_t BPC = 2 * K;  // 64-byte blocks per chunk (= per pipeline stage)
+  constexpr uint32_t RING = (uint32_t)(NST * K);  // tiles in the ring, consecutive in shared memory
   auto issue = [&](uint32_t c, int s) {
     if (lane == 0) {
       const uint64_t pos = (uint64_t)c * CH;
@@ -591,51 +595,68 @@ __device__ __forceinline__ void tile_stream_prefetch(const void* tmap, uint32_t 
 #pragma unroll
   for (int i = 0; i < NST; i++)
     if ((uint32_t)i < nch) issue((uint32_t)i, i);
-  const uint32_t nb_total = (uint32_t)(len >> 6), r = (uint32_t)(len & 63u);
-  const uint32_t total = nb_total + (r < 56 ? 1u : 2u);  // data blocks + padding block(s)
   const uint32_t swz = (uint32_t)(lane & 7);
-  const uint32_t lane_off = (uint32_t)lane * 128u;
-  int stage = 0;
-  uint32_t phase = 0, chunk = 0;
-  mbar_wait(s_bar, 0);
-  phase = 1u;
-  // loads block `blk` (data, or the tail block turned into padding) into w; steps to the next stage when blk is its first block
-  auto load = [&](uint32_t blk, uint32_t* w) {
-    uint32_t c = blk / BPC;
-    if (c > nch - 1u) c = nch - 1u;  // a second padding block may lie one block past the last chunk: nothing is read for it
-    if (c != chunk) {  // warp-uniform; every block of the old stage is in registers or done: give the stage back
-      __syncwarp();
-      fence_proxy_async_smem();
-      if (chunk + NST < nch) issue(chunk + NST, stage);
-      if (++stage == NST) stage = 0;
-      mbar_wait(s_bar + 8 * stage, (phase >> stage) & 1u);
-      phase ^= 1u << stage;
-      chunk = c;
-    }
-    const uint32_t bb_raw = blk - c * BPC;
-    const uint32_t bb = bb_raw < BPC ? bb_raw : 0u;
-    const uint32_t a = s_tiles + stage * G::STAGE_BYTES + lane_off + (bb >> 1) * G::TILE;
-    const uint32_t q0 = (bb & 1u) * 4u;
+  const uint32_t lane_base = s_tiles + (uint32_t)lane * 128u;
+  // 16 words of half `half` (0 | 1) of ring tile `t`
+  auto load_half = [&](uint32_t t, uint32_t half, uint32_t* w) {
+    const uint32_t a = lane_base + t * G::TILE;
 #pragma unroll
     for (int q = 0; q < 4; q++) {
-      uint4 v = lds128(a + (((q0 + q) ^ swz) << 4));
+      uint4 v = lds128(a + (((half * 4u + q) ^ swz) << 4));
       w[4 * q] = v.x; w[4 * q + 1] = v.y; w[4 * q + 2] = v.z; w[4 * q + 3] = v.w;
     }
-    if (blk >= nb_total) pad_block<A>(w, blk - nb_total, r, len);
     if (A::BE) {
 #pragma unroll
       for (int i = 0; i < 16; i++) w[i] = bswap(w[i]);
     }
   };
+  int stage = 0;
+  uint32_t phase = 0;
+  mbar_wait(s_bar, 0u);  // chunk 0 (whole, or the tail chunk of a short message)
+  phase = 1u;
   uint32_t wa[16], wb[16];
-  load(0u, wa);
+  const uint32_t nfull = nch - 1u;  // whole chunks; chunk nch-1 is partial (possibly empty) and carries the padding
+  if (nfull) load_half(0u, 0u, wa);
+  for (uint32_t c = 0; c < nfull; c++) {
+    int next = stage + 1;
+    if (next == NST) next = 0;
+    mbar_wait(s_bar + 8 * next, (phase >> next) & 1u);  // chunk c+1 <= nch-1 exists: the loop's last load reads its first block
+    phase ^= 1u << next;
+    uint32_t t = (uint32_t)stage * K;
 #pragma unroll 1
-  for (uint32_t blk = 0; blk < total; blk += 2) {
-    if (blk + 1 < total) load(blk + 1, wb);
-    A::compress(h, wa, one);
-    if (blk + 1 < total) {
-      if (blk + 2 < total) load(blk + 2, wa);
+    for (int i = 0; i < K; i++) {
+      load_half(t, 1u, wb);
+      A::compress(h, wa, one);
+      t = t + 1u == RING ? 0u : t + 1u;
+      load_half(t, 0u, wa);  // at i == K-1: the first block of the next stage (whose barrier has been waited for)
       A::compress(h, wb, one);
+    }
+    __syncwarp();
+    fence_proxy_async_smem();
+    if (c + NST < nch) issue(c + NST, stage);
+    stage = next;
+  }
+  // tail chunk: its barrier has been waited for (above, or at the top when the message has no whole chunk)
+  {
+    const uint32_t bytes = (uint32_t)(len - (uint64_t)nfull * CH);
+    const uint32_t nb = bytes >> 6, r = bytes & 63u;
+    const uint32_t nblk = nb + (r < 56 ? 1u : 2u);
+    const uint32_t t0 = (uint32_t)stage * K;
+    for (uint32_t b = 0; b < nblk; b++) {
+      uint32_t w[16];
+      const uint32_t bb = b < (uint32_t)(2 * K) ? b : 0u;  // padding block 1 past the stage: nothing to read
+      const uint32_t a = lane_base + (t0 + (bb >> 1)) * G::TILE;
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        uint4 v = lds128(a + ((((bb & 1u) * 4u + q) ^ swz) << 4));
+        w[4 * q] = v.x; w[4 * q + 1] = v.y; w[4 * q + 2] = v.z; w[4 * q + 3] = v.w;
+      }
+      if (b >= nb) pad_block<A>(w, b - nb, r, len);
+      if (A::BE) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) w[i] = bswap(w[i]);
+      }
+      A::compress(h, w, one);
     }
   }
 }

@@ -106,7 +106,6 @@ struct TileArgs {
   uint32_t* ok_bits;        // SHA-1 only, nullable
   uint32_t one;             // the value 1, opaque to the compiler (see add_fma)
   uint32_t salt;            // small grids: CTA b works on group (b + gridDim.x - salt) % gridDim.x, see spread_group
-  uint32_t lone;            // tile kernel: at most ~one warp per sub-partition (the prefetching stream pays off)
 };
 
 // A kernel with only a few CTAs always gets the same first SMs, so several such kernels running at once
@@ -145,7 +144,9 @@ __device__ __forceinline__ void finish_group(const TileArgs& p, uint32_t group, 
 
 // One warp = one CTA = 32 consecutive messages; used when messages are too few to fill the chip
 // (every group gets its own warp slot, and MD5 / SHA-256 kernels of one submit co-reside on an SM).
-template <class A, int K, int NST>
+// LONE: the warp has its sub-partition to itself (few large messages); the message then runs through
+// tile_stream_lone, whose loop overlaps a block's loads with the previous block's compression.
+template <class A, int K, int NST, bool LONE = false>
 __global__ void __launch_bounds__(32) digest_tile_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs p) {
   extern __shared__ __align__(1024) unsigned char smem[];
   using G = Tiles<K, NST>;
@@ -164,8 +165,8 @@ __global__ void __launch_bounds__(32) digest_tile_kernel(const __grid_constant__
   const uint32_t nch = (uint32_t)(p.len / G::CH) + 1u;
   uint32_t h[A::NS];
   A::init(h);
-  if (A::DLEN == 16 && p.lone) {  // MD5 chains with a sub-partition to themselves: latency-bound, see tile_stream_prefetch
-    tile_stream_prefetch<A, K, NST>(&tmap, group * 32u, p.len, nch, h, s_tiles, s_bar, lane, p.one);
+  if constexpr (LONE) {
+    tile_stream_lone<A, K, NST>(&tmap, group * 32u, p.len, nch, h, s_tiles, s_bar, lane, p.one);
   } else {
     PipeState ps;
     tile_segment<A, K, NST>(&tmap, group * 32u, p.len, 0u, nch, nch, h, s_tiles, s_bar, lane, ps, p.one);
@@ -458,7 +459,7 @@ struct TileOpts {
   int sliced_min_groups = 592;  // auto: use the sliced kernel from this many 32-message groups
   int tile_many_groups = 8192;  // auto: SHA-1 / SHA-256 batches with at least this many groups go back to one-warp CTAs
                                 // (many waves balance themselves and measured 1-12 % faster than the persistent kernel)
-  int md5_prefetch = 0;         // MD5 tile kernel with <= 4 groups per SM: load block b+1 before compressing block b
+  int md5_lone = 1;             // MD5 with at most one group per SM sub-partition: the run-ahead stream (tile_stream_lone)
   int fuse_md5_sha256 = 0;      // th_md5_sha256_batch: 1 = one chain + helper kernel does both where the plan is "assist" (measured slower: DESIGN.md §7)
   int ragged_rows = 1;          // per-lane kernels: 1 = cooperative cp.async row tiles, 0 = one bulk copy per lane
   int rows_variant[3] = {2, 2, 2};  // index into g_rows_variants per digest
@@ -473,13 +474,13 @@ constexpr int kRoomySmem = 112 * 1024;
 
 using tile_fn = cudaError_t (*)(const CUtensorMap&, const TileArgs&, uint32_t grid, uint32_t block, size_t smem, cudaStream_t);
 
-template <class A, int K, int NST>
+template <class A, int K, int NST, bool LONE = false>
 cudaError_t launch_tile(const CUtensorMap& m, const TileArgs& a, uint32_t grid, uint32_t, size_t pad, cudaStream_t st) {
   constexpr int smem = Tiles<K, NST>::WARP_BYTES + 8 * NST;
   static bool done[64] = {};
-  cudaError_t e0 = allow_smem(digest_tile_kernel<A, K, NST>, done, smem > kRoomySmem ? smem : kRoomySmem);
+  cudaError_t e0 = allow_smem(digest_tile_kernel<A, K, NST, LONE>, done, smem > kRoomySmem ? smem : kRoomySmem);
   if (e0 != cudaSuccess) return e0;
-  digest_tile_kernel<A, K, NST><<<grid, 32, pad > (size_t)smem ? pad : (size_t)smem, st>>>(m, a);
+  digest_tile_kernel<A, K, NST, LONE><<<grid, 32, pad > (size_t)smem ? pad : (size_t)smem, st>>>(m, a);
   return cudaGetLastError();
 }
 
@@ -526,6 +527,7 @@ struct Plan {
   uint32_t grid = 0, block = 32, workers = 0, segc = 0, nseg = 1, groups_per_cta = 0;
   int variant = -1;  // index into g_tile_variants
   size_t smem = 0;
+  bool lone_md5 = false;  // path 2, MD5, at most one group per sub-partition: digest_tile_kernel<Md5, 4, 3, LONE>
 };
 
 // Chooses the kernel for an equal-length, fixed-stride batch (path 1 = not eligible for tensor maps).
@@ -572,6 +574,9 @@ static Plan make_plan(int ai, uint64_t stride, uint64_t len, uint32_t n) {
   const TileVariant& v = g_tile_variants[g_opts.path == 0 && many ? g_sliced_selected[ai] : g_tile_selected[ai]];
   pl.path = 2; pl.k = v.k; pl.nst = v.nst; pl.grid = groups; pl.block = 32; pl.variant = int(&v - g_tile_variants);
   pl.smem = (size_t)v.k * v.nst * 4096 + 8 * v.nst;
+  if (ai == 1 && g_opts.md5_lone && groups <= 4u * (uint32_t)sms) {  // MD5 chains alone on their sub-partitions
+    pl.lone_md5 = true; pl.k = 4; pl.nst = 3; pl.smem = (size_t)4 * 3 * 4096 + 8 * 3;
+  }
   return pl;
 }
 
@@ -585,14 +590,13 @@ static int launch_uniform(int ai, const void* d_base, uint64_t stride, uint64_t 
   if (d_out_md5 && (pl.path != 4 || ai != 2)) return 1;
   CUtensorMap tmap;
   if (!make_tmap(&tmap, d_base, len, stride, n)) return 1;
-  TileArgs a{len, n, pl.segc, pl.nseg, d_out, d_out_md5, d_expected, d_ok_bits, 1u, 0u, 0u};
+  TileArgs a{len, n, pl.segc, pl.nseg, d_out, d_out_md5, d_expected, d_ok_bits, 1u, 0u};
   uint32_t grid = pl.grid;
   size_t pad = 0;
   if (pl.path != 3) {  // few CTAs: pad to one per SM and rotate by a per-launch salt (see spread_group)
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    a.lone = (pl.path == 2 && grid <= 4u * (uint32_t)sms && g_opts.md5_prefetch) ? 1u : 0u;
     if (grid <= (uint32_t)sms) {
       static std::atomic<uint32_t> launches{0};
       a.salt = (launches.fetch_add(1) * 37u) % (uint32_t)sms;
@@ -613,6 +617,10 @@ static int launch_uniform(int ai, const void* d_base, uint64_t stride, uint64_t 
       case 4: e = ai == 0 ? launch_assist<Sha1, 2, 4, 2>(tmap, a, grid, 64, pad, st) : launch_assist<Sha256, 2, 4, 2>(tmap, a, grid, 64, pad, st); break;
       default: e = ai == 0 ? launch_assist<Sha1, 2, 2, 4>(tmap, a, grid, 64, pad, st) : launch_assist<Sha256, 2, 2, 4>(tmap, a, grid, 64, pad, st); break;
     }
+    return e == cudaSuccess ? TH_OK : TH_ECUDA;
+  }
+  if (pl.lone_md5) {
+    const cudaError_t e = launch_tile<Md5, 4, 3, true>(tmap, a, grid, 32, pad, st);
     return e == cudaSuccess ? TH_OK : TH_ECUDA;
   }
   const TileVariant& v = g_tile_variants[pl.variant];
@@ -836,7 +844,7 @@ int th_set_option(const char* name, long long value) {
   if (k == "tile_many_groups") { if (value < 1) return TH_EINVAL; th::g_opts.tile_many_groups = (int)value; return TH_OK; }
   if (k == "sliced_min_groups") { if (value < 1) return TH_EINVAL; th::g_opts.sliced_min_groups = (int)value; return TH_OK; }
   if (k == "ragged_rows") { if (value < 0 || value > 1) return TH_EINVAL; th::g_opts.ragged_rows = (int)value; return TH_OK; }
-  if (k == "md5_prefetch") { if (value < 0 || value > 1) return TH_EINVAL; th::g_opts.md5_prefetch = (int)value; return TH_OK; }
+  if (k == "md5_lone") { if (value < 0 || value > 1) return TH_EINVAL; th::g_opts.md5_lone = (int)value; return TH_OK; }
   if (k == "fuse_md5_sha256") { if (value < 0 || value > 1) return TH_EINVAL; th::g_opts.fuse_md5_sha256 = (int)value; return TH_OK; }
   if (k == "rows_variant") {
     if (value < 0 || value >= th::kNumRowsVariants) return TH_EINVAL;
@@ -874,8 +882,8 @@ int th_plan(uint32_t alg, uint64_t len, uint64_t stride, uint32_t n, char* out, 
              "assist: %u CTAs x (chain warp + schedule-helper warp), TMA 2-D {128B x 32 msgs} x %d tiles x %d stages, "
              "4-slot schedule ring, smem %zu B", pl.grid, pl.k, pl.nst, pl.smem);
   } else if (pl.path == 2) {
-    snprintf(out, cap, "tile: one-warp CTAs, TMA 2-D {128B x 32 msgs} x %d tiles x %d stages, grid %u, smem %zu B", pl.k,
-             pl.nst, pl.grid, pl.smem);
+    snprintf(out, cap, "tile%s: one-warp CTAs, TMA 2-D {128B x 32 msgs} x %d tiles x %d stages, grid %u, smem %zu B",
+             pl.lone_md5 ? " (lone chains: loads of the next block run ahead of each compression)" : "", pl.k, pl.nst, pl.grid, pl.smem);
   } else {
     snprintf(out, cap,
              "sliced: persistent %u CTAs x %u warps, TMA 2-D {128B x 32 msgs} x %d tiles x %d stages, <=%u groups/CTA, "
