@@ -252,7 +252,8 @@ def make_step(E, data, n, ln, names, outs, expected=None, ok=None):
         assert rc == 0, (name, rc)
 
     if set(names) == {"md5", "sha256"} and L.th_md5_sha256_fused(ln, ln, n) == 1:
-        # few large parts: ONE kernel, the SHA-256 chain's helper warp runs the MD5 chain too (what th_submit launches)
+        # few large parts: ONE launch — SHA-256 chain, its schedule helper and an MD5 chain per group, each warp on a
+        # sub-partition of its own (digest_parts_kernel; what th_submit launches for MD5 | SHA-256)
         def fused_step():
             rc = L.th_md5_sha256_batch(base, ln, ln, n, outs["md5"].data_ptr(), outs["sha256"].data_ptr(), E.sp)
             assert rc == 0, rc
@@ -836,7 +837,7 @@ def _plan(algs, ln, n):
     from downloader_b200 import _capi
     names = algs.split("+")
     if set(names) == {"md5", "sha256"} and _capi.lib().th_md5_sha256_fused(ln, ln, n) == 1:
-        return "fused: " + _capi.plan(4, ln, ln, n) + "; the helper warp also runs the MD5 chain of the same parts (one launch, parts read once)"
+        return "parts: one launch, per group a SHA-256 chain warp + schedule-helper warp + MD5 chain warp on separate sub-partitions; SHA-256 half: " + _capi.plan(4, ln, ln, n)
     if len(names) == 1:
         return _capi.plan(ALG_BIT[names[0]], ln, ln, n)
     return {a: _capi.plan(ALG_BIT[a], ln, ln, n) for a in names}

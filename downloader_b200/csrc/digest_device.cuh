@@ -725,7 +725,13 @@ struct Assist<Sha256> {
   //   V = 2  10 ALU + 8 FMA: a' as an IMAD pair as well
   //   V = 3  10 ALU + 6 FMA: e' = d + t1 (one IMAD after t1, no separate d + hh + wk), a' as an IMAD pair
   //   V = 4  11 ALU + 4 FMA: as 3 but a' = IADD3
-  template <int V = 1, int KH_ = KH>
+  // TRIPS: the 64 rounds as a loop of TRIPS trips (the working variables rotate with period 8, so a trip of 16 or 32
+  // rounds ends where it began): 17 KB of code unrolled (TRIPS = 1), 8.7 KB with 2 trips, 4.5 KB with 4.  The chain
+  // warp's loop, the helper's and — when MD5 of the same parts runs beside them, as a third warp or as its own kernel —
+  // the MD5 loop share the SM's 32 KB instruction cache; with the rounds unrolled they add up to 37 KB and everything on
+  // the SM slows down by a quarter (MD5 + SHA-256 over 4,096 x 16 MiB parts: 289 ms against 227 ms for SHA-256 alone,
+  // although every warp had a sub-partition to itself).
+  template <int V = 1, int KH_ = KH, int TRIPS = 1>
   __device__ static __forceinline__ void rounds(uint32_t* h, const uint4* src, uint32_t one) {
     constexpr uint32_t K[64] = {
         0x428a2f98, 0x71374491, 0xb5c0fbcf, 0xe9b5dba5, 0x3956c25b, 0x59f111f1, 0x923f82a4, 0xab1c5ed5,
@@ -736,97 +742,65 @@ struct Assist<Sha256> {
         0xa2bfe8a1, 0xa81a664b, 0xc24b8b70, 0xc76c51a3, 0xd192e819, 0xd6990624, 0xf40e3585, 0x106aa070,
         0x19a4c116, 0x1e376c08, 0x2748774c, 0x34b0bcb5, 0x391c0cb3, 0x4ed8aa4a, 0x5b9cca4f, 0x682e6ff3,
         0x748f82ee, 0x78a5636f, 0x84c87814, 0x8cc70208, 0x90befffa, 0xa4506ceb, 0xbef9a3f7, 0xc67178f2};
+    static_assert(TRIPS == 1 || KH_ == 64, "the rolled loop has one body for all trips: the constants must come from the helper");
+    static_assert(TRIPS == 1 || TRIPS == 2 || TRIPS == 4, "trips of 64, 32 or 16 rounds");
     uint32_t a = h[0], b = h[1], c = h[2], d = h[3], e = h[4], f = h[5], g = h[6], hh = h[7];
+    // one round; t only matters (as a compile-time constant) when the chain warp adds the round constant itself
+    auto round = [&](uint32_t wk, int t) {
+      const uint32_t S1 = lop3<LUT_XOR3>(rotr(e, 6), rotr(e, 11), rotr(e, 25));
+      const uint32_t ch = lop3<LUT_CH>(e, f, g);
+      const uint32_t S0 = lop3<LUT_XOR3>(rotr(a, 2), rotr(a, 13), rotr(a, 22));
+      const uint32_t mj = lop3<LUT_MAJ>(a, b, c);
+      // hh + K[t] + w: nothing of this round's inputs; from word KH on the constant is added here (hh is four rounds old)
+      const uint32_t p = t >= KH_ ? add_fma(add_fma(hh, K[t & 63], one), wk, one) : add_fma(hh, wk, one);
+      uint32_t t1, en, an;
+      if (V == 0) {
+        const uint32_t dp = add_fma(d, p, one);
+        t1 = p + ch + S1;
+        en = dp + ch + S1;
+        an = t1 + S0 + mj;
+      } else if (V == 1 || V == 2) {
+        const uint32_t dp = add_fma(d, p, one);
+        t1 = add_fma(add_fma(p, ch, one), S1, one);
+        en = add_fma(add_fma(dp, ch, one), S1, one);
+        an = V == 1 ? t1 + S0 + mj : add_fma(t1, add_fma(S0, mj, one), one);
+      } else {
+        t1 = add_fma(add_fma(p, ch, one), S1, one);
+        en = add_fma(d, t1, one);
+        an = V == 4 ? t1 + S0 + mj : add_fma(t1, add_fma(S0, mj, one), one);
+      }
+      hh = g; g = f; f = e; e = en; d = c; c = b; b = a; a = an;
+    };
+    if (TRIPS > 1) {
+      // The next trip's words are loaded into each half of the register window as soon as the current trip is done
+      // with it, so no trip starts by waiting for its first LDS (that wait, ~35 clocks per trip, is most of what a
+      // plain rolled loop costs: 1,833 clocks per block with 4 trips, 1,752 with this, 1,631 fully unrolled).
+      constexpr int Q = 16 / TRIPS, HALF = Q / 2;  // 16-byte quads per trip
+      uint4 v[Q];
 #pragma unroll
-    for (int q = 0; q < 16; q++) {
-      const uint4 v = src[q * 32];
-      const uint32_t wk[4] = {v.x, v.y, v.z, v.w};
+      for (int q = 0; q < Q; q++) v[q] = src[q * 32];
+#pragma unroll 1
+      for (int trip = 0; trip < TRIPS; trip++) {
+        const uint4* nx = src + ((trip + 1) % TRIPS) * (Q * 32);  // the last trip re-reads the first quads: harmless, unused
 #pragma unroll
-      for (int j = 0; j < 4; j++) {
-        const uint32_t S1 = lop3<LUT_XOR3>(rotr(e, 6), rotr(e, 11), rotr(e, 25));
-        const uint32_t ch = lop3<LUT_CH>(e, f, g);
-        const uint32_t S0 = lop3<LUT_XOR3>(rotr(a, 2), rotr(a, 13), rotr(a, 22));
-        const uint32_t mj = lop3<LUT_MAJ>(a, b, c);
-        // hh + K[t] + w: nothing of this round's inputs; from word KH on the constant is added here (hh is four rounds old)
-        const uint32_t p = 4 * q + j >= KH_ ? add_fma(add_fma(hh, K[4 * q + j], one), wk[j], one) : add_fma(hh, wk[j], one);
-        uint32_t t1, en, an;
-        if (V == 0) {
-          const uint32_t dp = add_fma(d, p, one);
-          t1 = p + ch + S1;
-          en = dp + ch + S1;
-          an = t1 + S0 + mj;
-        } else if (V == 1 || V == 2) {
-          const uint32_t dp = add_fma(d, p, one);
-          t1 = add_fma(add_fma(p, ch, one), S1, one);
-          en = add_fma(add_fma(dp, ch, one), S1, one);
-          an = V == 1 ? t1 + S0 + mj : add_fma(t1, add_fma(S0, mj, one), one);
-        } else {
-          t1 = add_fma(add_fma(p, ch, one), S1, one);
-          en = add_fma(d, t1, one);
-          an = V == 4 ? t1 + S0 + mj : add_fma(t1, add_fma(S0, mj, one), one);
-        }
-        hh = g; g = f; f = e; e = en; d = c; c = b; b = a; a = an;
+        for (int q = 0; q < HALF; q++) { round(v[q].x, 0); round(v[q].y, 0); round(v[q].z, 0); round(v[q].w, 0); }
+#pragma unroll
+        for (int q = 0; q < HALF; q++) v[q] = nx[q * 32];
+#pragma unroll
+        for (int q = HALF; q < Q; q++) { round(v[q].x, 0); round(v[q].y, 0); round(v[q].z, 0); round(v[q].w, 0); }
+#pragma unroll
+        for (int q = HALF; q < Q; q++) v[q] = nx[q * 32];
+      }
+    } else {
+#pragma unroll
+      for (int q = 0; q < 16; q++) {
+        const uint4 v = src[q * 32];
+        round(v.x, 4 * q); round(v.y, 4 * q + 1); round(v.z, 4 * q + 2); round(v.w, 4 * q + 3);
       }
     }
     h[0] += a; h[1] += b; h[2] += c; h[3] += d; h[4] += e; h[5] += f; h[6] += g; h[7] += hh;
   }
 };
-
-// One MD5 step with a run-time-looking index that is a constant after full unrolling (the fused helper below
-// interleaves MD5 step t with schedule word t in SOURCE order; ptxas keeps that order where latencies allow).
-// s[0..3] = a, b, c, d of RFC 1321; step t rotates the roles: its "a" is s[(4 - t) & 3].
-__device__ __forceinline__ void md5_step_at(uint32_t* s, const uint32_t* m, int t, uint32_t one) {
-  constexpr uint32_t T[64] = {
-      0xd76aa478, 0xe8c7b756, 0x242070db, 0xc1bdceee, 0xf57c0faf, 0x4787c62a, 0xa8304613, 0xfd469501,
-      0x698098d8, 0x8b44f7af, 0xffff5bb1, 0x895cd7be, 0x6b901122, 0xfd987193, 0xa679438e, 0x49b40821,
-      0xf61e2562, 0xc040b340, 0x265e5a51, 0xe9b6c7aa, 0xd62f105d, 0x02441453, 0xd8a1e681, 0xe7d3fbc8,
-      0x21e1cde6, 0xc33707d6, 0xf4d50d87, 0x455a14ed, 0xa9e3e905, 0xfcefa3f8, 0x676f02d9, 0x8d2a4c8a,
-      0xfffa3942, 0x8771f681, 0x6d9d6122, 0xfde5380c, 0xa4beea44, 0x4bdecfa9, 0xf6bb4b60, 0xbebfbc70,
-      0x289b7ec6, 0xeaa127fa, 0xd4ef3085, 0x04881d05, 0xd9d4d039, 0xe6db99e5, 0x1fa27cf8, 0xc4ac5665,
-      0xf4292244, 0x432aff97, 0xab9423a7, 0xfc93a039, 0x655b59c3, 0x8f0ccc92, 0xffeff47d, 0x85845dd1,
-      0x6fa87e4f, 0xfe2ce6e0, 0xa3014314, 0x4e0811a1, 0xf7537e82, 0xbd3af235, 0x2ad7d2bb, 0xeb86d391};
-  constexpr int S[16] = {7, 12, 17, 22, 5, 9, 14, 20, 4, 11, 16, 23, 6, 10, 15, 21};
-  const int r = t >> 4;
-  const int g = r == 0 ? t : r == 1 ? (5 * t + 1) & 15 : r == 2 ? (3 * t + 5) & 15 : (7 * t) & 15;
-  uint32_t& a = s[(4 - t) & 3];
-  const uint32_t b = s[(5 - t) & 3], c = s[(6 - t) & 3], d = s[(7 - t) & 3];
-  const uint32_t f = r == 0 ? lop3<LUT_CH>(b, c, d) : r == 1 ? lop3<LUT_CH>(d, b, c)
-                   : r == 2 ? lop3<LUT_XOR3>(b, c, d) : lop3<LUT_MD5I>(b, c, d);
-  const uint32_t akm = a + add_fma(m[g], T[t], one);
-  a = b + rotl(akm + f, S[(r << 2) | (t & 3)]);
-}
-
-// Helper body of the fused MD5 + SHA-256 kernel: SHA-256 schedule word t (as Assist<Sha256>::expand<V>) and MD5 step t,
-// alternately, t = 0..63.  w: 16 big-endian words (rolling window, destroyed); m: the same block as 16 little-endian
-// words with MD5's padding; hm: MD5 chaining value.
-template <int V = 0, int KH_ = Assist<Sha256>::KH>
-__device__ __forceinline__ void expand_sha256_with_md5(uint32_t* w, const uint32_t* m, uint32_t* hm, uint32_t dst, uint32_t one) {
-  constexpr uint32_t K[64] = {
-      0x428a2f98, 0x71374491, 0xb5c0fbcf, 0xe9b5dba5, 0x3956c25b, 0x59f111f1, 0x923f82a4, 0xab1c5ed5,
-      0xd807aa98, 0x12835b01, 0x243185be, 0x550c7dc3, 0x72be5d74, 0x80deb1fe, 0x9bdc06a7, 0xc19bf174,
-      0xe49b69c1, 0xefbe4786, 0x0fc19dc6, 0x240ca1cc, 0x2de92c6f, 0x4a7484aa, 0x5cb0a9dc, 0x76f988da,
-      0x983e5152, 0xa831c66d, 0xb00327c8, 0xbf597fc7, 0xc6e00bf3, 0xd5a79147, 0x06ca6351, 0x14292967,
-      0x27b70a85, 0x2e1b2138, 0x4d2c6dfc, 0x53380d13, 0x650a7354, 0x766a0abb, 0x81c2c92e, 0x92722c85,
-      0xa2bfe8a1, 0xa81a664b, 0xc24b8b70, 0xc76c51a3, 0xd192e819, 0xd6990624, 0xf40e3585, 0x106aa070,
-      0x19a4c116, 0x1e376c08, 0x2748774c, 0x34b0bcb5, 0x391c0cb3, 0x4ed8aa4a, 0x5b9cca4f, 0x682e6ff3,
-      0x748f82ee, 0x78a5636f, 0x84c87814, 0x8cc70208, 0x90befffa, 0xa4506ceb, 0xbef9a3f7, 0xc67178f2};
-  uint32_t s[4] = {hm[0], hm[1], hm[2], hm[3]};
-  uint32_t o[4];
-#pragma unroll
-  for (int t = 0; t < 64; t++) {
-    if (t >= 16) {
-      uint32_t x = w[(t - 15) & 15], y = w[(t - 2) & 15];
-      uint32_t s0 = lop3<LUT_XOR3>(rotr(x, 7), rotr(x, 18), x >> 3);
-      uint32_t s1 = lop3<LUT_XOR3>(rotr(y, 17), rotr(y, 19), y >> 10);
-      if (V == 0) w[t & 15] = w[t & 15] + s0 + w[(t - 7) & 15] + s1;
-      else w[t & 15] = add_fma(add_fma(w[t & 15], w[(t - 7) & 15], one), add_fma(s0, s1, one), one);
-    }
-    o[t & 3] = t >= KH_ ? w[t & 15] : V == 0 ? w[t & 15] + K[t] : add_fma(w[t & 15], K[t], one);
-    md5_step_at(s, m, t, one);
-    if ((t & 3) == 3) sts128(dst + (t >> 2) * 512, o[0], o[1], o[2], o[3]);
-  }
-  hm[0] += s[0]; hm[1] += s[1]; hm[2] += s[2]; hm[3] += s[3];
-}
 
 template <>
 struct Assist<Sha1> {
@@ -875,17 +849,11 @@ struct Assist<Sha1> {
 
 // Helper warp: streams the group's message through the TMA tiles (as tile_segment does) and, instead of
 // compressing, expands every block (padding blocks included) into schedule-ring slot (block % SS).
-//
-// MD5_TOO: the helper also runs the MD5 chain of the same messages (hm = its chaining value).  The upload path wants
-// MD5 and SHA-256 of every part (lib/upload.js:45 -> minio getHashSummer), and the helper has the slack: the chain
-// warp needs ~1,850 cycles per block for its 64 rounds, the schedule expansion keeps the helper busy for ~1,200, and
-// an MD5 block is ~260 instructions whose 3-deep dependent chain (latency-bound when it runs alone) interleaves with
-// the expansion's independent work in the same instruction stream.  The block's words are already in the helper's
-// registers, so MD5 costs no second pass over HBM, no second kernel and no sub-partition of its own.
-template <class A, int K, int NST, int SS, bool MD5_TOO = false>
+// bar0: first of the 2*SS named barriers this chain / helper pair hands slots over with (a CTA may hold two pairs).
+template <class A, int K, int NST, int SS>
 __device__ __forceinline__ void assist_produce(const void* tmap, uint32_t row0, uint64_t len, uint32_t nch,
                                                uint32_t s_tiles, uint32_t s_bar, uint32_t s_ring, int lane,
-                                               uint32_t one, uint32_t* hm = nullptr) {
+                                               uint32_t one, int bar0 = 1) {
   using G = Tiles<K, NST>;
   constexpr int CH = G::CH;
   constexpr uint32_t SLOT = Assist<A>::WPB * 128;
@@ -925,21 +893,12 @@ __device__ __forceinline__ void assist_produce(const void* tmap, uint32_t row0, 
         uint4 v = lds128(a + (((q0 + q) ^ swz) << 4));
         w[4 * q] = v.x; w[4 * q + 1] = v.y; w[4 * q + 2] = v.z; w[4 * q + 3] = v.w;
       }
-      uint32_t m[16];  // the same block as MD5 sees it: little-endian words, MD5's own padding
-      if (MD5_TOO) {
-#pragma unroll
-        for (int i = 0; i < 16; i++) m[i] = w[i];
-      }
-      if (b >= nb) {
-        pad_block<A>(w, b - nb, r, len);
-        if (MD5_TOO) pad_block<Md5>(m, b - nb, r, len);
-      }
+      if (b >= nb) pad_block<A>(w, b - nb, r, len);
 #pragma unroll
       for (int i = 0; i < 16; i++) w[i] = bswap(w[i]);
-      if (produced >= (uint32_t)SS) nb_sync(1 + SS + slot);  // wait until the chain warp has drained this slot
-      if (MD5_TOO) expand_sha256_with_md5(w, m, hm, s_ring + slot * SLOT + lane * 16, one);  // schedule word t / MD5 step t, alternately
-      else Assist<A>::expand(w, s_ring + slot * SLOT + lane * 16, one);
-      nb_arrive(1 + slot);
+      if (produced >= (uint32_t)SS) nb_sync(bar0 + SS + slot);  // wait until the chain warp has drained this slot
+      Assist<A>::expand(w, s_ring + slot * SLOT + lane * 16, one);
+      nb_arrive(bar0 + slot);
       produced++;
       if (++slot == SS) slot = 0;
     }
@@ -951,16 +910,17 @@ __device__ __forceinline__ void assist_produce(const void* tmap, uint32_t row0, 
 }
 
 // Chain warp: consumes `total` expanded blocks.
-template <class A, int SS>
+template <class A, int SS, int TRIPS = 1>
 __device__ __forceinline__ void assist_consume(uint32_t total, uint32_t* h, const unsigned char* ring, int lane,
-                                               uint32_t one) {
+                                               uint32_t one, int bar0 = 1) {
   constexpr uint32_t SLOT = Assist<A>::WPB * 128;
   int slot = 0;
 #pragma unroll 1  // one copy of the rounds: two would not fit the 32 KB instruction cache beside the helper's loop
   for (uint32_t i = 0; i < total; i++) {
-    nb_sync(1 + slot);
-    Assist<A>::rounds(h, reinterpret_cast<const uint4*>(ring + slot * SLOT) + lane, one);
-    if (i + SS < total) nb_arrive(1 + SS + slot);  // hand the slot back (only if the helper will reuse it)
+    nb_sync(bar0 + slot);
+    if constexpr (TRIPS == 1) Assist<A>::rounds(h, reinterpret_cast<const uint4*>(ring + slot * SLOT) + lane, one);
+    else Assist<A>::template rounds<1, Assist<A>::KH, TRIPS>(h, reinterpret_cast<const uint4*>(ring + slot * SLOT) + lane, one);
+    if (i + SS < total) nb_arrive(bar0 + SS + slot);  // hand the slot back (only if the helper will reuse it)
     if (++slot == SS) slot = 0;
   }
 }

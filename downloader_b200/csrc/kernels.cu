@@ -101,7 +101,7 @@ struct TileArgs {
   uint32_t segc;            // sliced kernel: chunks per segment
   uint32_t nseg;            // sliced kernel: segments per message
   uint8_t* out;
-  uint8_t* out_md5;         // chain + helper kernel with MD5_TOO: the MD5 digests the helper warp produces
+  uint8_t* out_md5;         // digest_parts_kernel: the MD5 digests (out holds the SHA-256 ones)
   const uint8_t* expected;  // SHA-1 only, nullable
   uint32_t* ok_bits;        // SHA-1 only, nullable
   uint32_t one;             // the value 1, opaque to the compiler (see add_fma)
@@ -175,8 +175,7 @@ __global__ void __launch_bounds__(32) digest_tile_kernel(const __grid_constant__
 }
 
 // Few, large messages (fewer groups than SM sub-partitions): chain warp + schedule helper warp per group.
-// MD5_TOO (SHA-256 only): the helper warp also runs the MD5 chain of the same parts (see assist_produce).
-template <class A, int K, int NST, int SS, bool MD5_TOO = false>
+template <class A, int K, int NST, int SS>
 __global__ void __launch_bounds__(64) digest_assist_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs p) {
   extern __shared__ __align__(1024) unsigned char smem[];
   using G = Tiles<K, NST>;
@@ -197,18 +196,82 @@ __global__ void __launch_bounds__(64) digest_assist_kernel(const __grid_constant
   const uint32_t r = (uint32_t)(p.len & 63u);
   const uint32_t total = (uint32_t)(p.len >> 6) + (r < 56 ? 1u : 2u);
   if (warp == 1) {
-    uint32_t hm[4];
-    Md5::init(hm);
-    assist_produce<A, K, NST, SS, MD5_TOO>(&tmap, group * 32u, p.len, nch, s_tiles, s_bar, s_ring, lane, p.one, hm);
-    if (MD5_TOO) {
-      const uint32_t idx = group * 32u + lane;
-      if (idx < p.n) store_digest<Md5>(p.out_md5 + (size_t)idx * Md5::DLEN, hm);
-    }
+    assist_produce<A, K, NST, SS>(&tmap, group * 32u, p.len, nch, s_tiles, s_bar, s_ring, lane, p.one);
   } else {
     uint32_t h[A::NS];
     A::init(h);
     assist_consume<A, SS>(total, h, smem + G::WARP_BYTES, lane, p.one);
     finish_group<A>(p, group, lane, h);
+  }
+}
+
+// MD5 AND SHA-256 of few large messages — the digests an S3 part needs (lib/upload.js:45 -> [dep] minio getHashSummer)
+// — in ONE launch whose CTAs place every chain on a sub-partition of its own.  Launched as two kernels, the MD5 warps
+// land wherever the block scheduler puts them: next to a SHA-256 chain warp (which needs every ALU slot of its
+// sub-partition) as often as next to a helper warp or on an idle sub-partition — 4,096 x 16 MiB parts measured anything
+// from 246 to 294 ms from run to run and launch order to launch order, against 227 ms for SHA-256 alone.  Warps of one
+// CTA are dealt to the four sub-partitions in order, so here the roles are fixed by warp index:
+//   GP = 1 (up to one group per SM):  warp 0 SHA-256 chain, 1 schedule helper, 2 MD5 chain            (3 sub-partitions)
+//   GP = 2 (up to two groups per SM): warps 0,1 the two SHA-256 chains, 2,3 their helpers, 4,5 exit at once,
+//                                     6,7 the two MD5 chains — which share sub-partitions 2,3 with the helpers, the
+//                                     warps with issue slots to spare, never with a chain warp.
+// The MD5 warp streams the parts through its own tiles (tile_stream_lone); it reads the same bytes a moment after or
+// before the helper does, so the second read is served by L2 (dram__bytes_read stays at the message bytes).
+template <int K, int NST, int SS, int GP, int TRIPS>
+__global__ void __launch_bounds__(GP == 1 ? 96 : 256) digest_parts_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs p) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  using G = Tiles<K, NST>;
+  using GM = Tiles<4, 3>;  // the MD5 warp's own ring (tile_stream_lone wants three stages)
+  constexpr uint32_t RING_BYTES = SS * Assist<Sha256>::WPB * 128;
+  constexpr uint32_t PER_GROUP = G::WARP_BYTES + RING_BYTES + GM::WARP_BYTES;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // role and which of the CTA's groups this warp serves
+  int role, g;  // role 0 chain, 1 helper, 2 md5, 3 none
+  if (GP == 1) { role = warp; g = 0; }
+  else { role = warp < 2 ? 0 : warp < 4 ? 1 : warp < 6 ? 3 : 2; g = warp & 1; }
+  const uint32_t groups = (p.n + 31u) / 32u;
+  uint32_t slot = blockIdx.x;  // CTA -> slot of GP groups, rotated by the per-launch salt like spread_group
+  const uint32_t slots = (groups + GP - 1) / GP;
+  if (gridDim.x > slots) {
+    slot = blockIdx.x + gridDim.x - p.salt;
+    if (slot >= gridDim.x) slot -= gridDim.x;
+  }
+  const uint32_t group = slot * GP + (uint32_t)g;
+  const bool active = slot < slots && group < groups && role != 3;
+  unsigned char* base = smem + (size_t)g * PER_GROUP;
+  const uint32_t s_tiles = smem_u32(base);
+  const uint32_t s_ring = s_tiles + G::WARP_BYTES;
+  const uint32_t s_md5 = s_ring + RING_BYTES;
+  const uint32_t s_bar = smem_u32(smem) + GP * PER_GROUP + (uint32_t)g * 64u;  // per group: NST helper + 3 MD5 mbarriers
+  if (active && lane == 0 && role != 0) {
+    if (role == 1) {
+      prefetch_tmap(&tmap);
+#pragma unroll
+      for (int s = 0; s < NST; s++) mbar_init(s_bar + 8 * s, 1);
+    } else {
+#pragma unroll
+      for (int s = 0; s < 3; s++) mbar_init(s_bar + 32 + 8 * s, 1);
+    }
+    mbar_init_fence();
+  }
+  __syncthreads();
+  if (!active) return;
+  const uint32_t r = (uint32_t)(p.len & 63u);
+  const uint32_t total = (uint32_t)(p.len >> 6) + (r < 56 ? 1u : 2u);
+  const int bar0 = 1 + g * 2 * SS;
+  if (role == 1) {
+    assist_produce<Sha256, K, NST, SS>(&tmap, group * 32u, p.len, (uint32_t)(p.len / G::CH) + 1u, s_tiles, s_bar, s_ring, lane, p.one, bar0);
+  } else if (role == 0) {
+    uint32_t h[Sha256::NS];
+    Sha256::init(h);
+    assist_consume<Sha256, SS, TRIPS>(total, h, base + G::WARP_BYTES, lane, p.one, bar0);  // rolled rounds: see Assist<Sha256>::rounds
+    finish_group<Sha256>(p, group, lane, h);
+  } else {
+    uint32_t h[Md5::NS];
+    Md5::init(h);
+    tile_stream_lone<Md5, 4, 3>(&tmap, group * 32u, p.len, (uint32_t)(p.len / GM::CH) + 1u, h, s_md5, s_bar + 32, lane, p.one);
+    const uint32_t idx = group * 32u + lane;
+    if (idx < p.n) store_digest<Md5>(p.out_md5 + (size_t)idx * Md5::DLEN, h);
   }
 }
 
@@ -460,7 +523,8 @@ struct TileOpts {
   int tile_many_groups = 8192;  // auto: SHA-1 / SHA-256 batches with at least this many groups go back to one-warp CTAs
                                 // (many waves balance themselves and measured 1-12 % faster than the persistent kernel)
   int md5_lone = 1;             // MD5 with at most one group per SM sub-partition: the run-ahead stream (tile_stream_lone)
-  int fuse_md5_sha256 = 0;      // th_md5_sha256_batch: 1 = one chain + helper kernel does both where the plan is "assist" (measured slower: DESIGN.md §7)
+  int parts_trips = 4;          // digest_parts_kernel: SHA-256 rounds as 4 trips of 16 (4.5 KB of code; measured 243 ms per 16 MiB part) or 2 of 32 (8.7 KB; 262 ms)
+  int fuse_md5_sha256 = 1;      // th_md5_sha256_batch: 1 = one launch (digest_parts_kernel) where the SHA-256 plan is "assist"
   int ragged_rows = 1;          // per-lane kernels: 1 = cooperative cp.async row tiles, 0 = one bulk copy per lane
   int rows_variant[3] = {2, 2, 2};  // index into g_rows_variants per digest
 };
@@ -493,13 +557,27 @@ cudaError_t launch_sliced(const CUtensorMap& m, const TileArgs& a, uint32_t grid
   return cudaGetLastError();
 }
 
-template <class A, int K, int NST, int SS, bool MD5_TOO = false>
+template <class A, int K, int NST, int SS>
 cudaError_t launch_assist(const CUtensorMap& m, const TileArgs& a, uint32_t grid, uint32_t, size_t pad, cudaStream_t st) {
   constexpr int smem = Tiles<K, NST>::WARP_BYTES + SS * Assist<A>::WPB * 128 + 8 * NST;
   static bool done[64] = {};
-  cudaError_t e0 = allow_smem(digest_assist_kernel<A, K, NST, SS, MD5_TOO>, done, smem > kRoomySmem ? smem : kRoomySmem);
+  cudaError_t e0 = allow_smem(digest_assist_kernel<A, K, NST, SS>, done, smem > kRoomySmem ? smem : kRoomySmem);
   if (e0 != cudaSuccess) return e0;
-  digest_assist_kernel<A, K, NST, SS, MD5_TOO><<<grid, 64, pad > (size_t)smem ? pad : (size_t)smem, st>>>(m, a);
+  digest_assist_kernel<A, K, NST, SS><<<grid, 64, pad > (size_t)smem ? pad : (size_t)smem, st>>>(m, a);
+  return cudaGetLastError();
+}
+
+template <int K, int NST, int SS, int GP>
+constexpr int parts_smem() { return GP * (Tiles<K, NST>::WARP_BYTES + SS * Assist<Sha256>::WPB * 128 + Tiles<4, 3>::WARP_BYTES) + GP * 64; }
+
+template <int K, int NST, int SS, int GP, int TRIPS>
+cudaError_t launch_parts(const CUtensorMap& m, const TileArgs& a, uint32_t grid, size_t pad, cudaStream_t st) {
+  constexpr int smem = parts_smem<K, NST, SS, GP>();
+  static_assert(smem <= 227 * 1024, "digest_parts_kernel: shared memory");
+  static bool done[64] = {};
+  cudaError_t e0 = allow_smem(digest_parts_kernel<K, NST, SS, GP, TRIPS>, done, smem > kRoomySmem ? smem : kRoomySmem);
+  if (e0 != cudaSuccess) return e0;
+  digest_parts_kernel<K, NST, SS, GP, TRIPS><<<grid, GP == 1 ? 96 : 256, pad > (size_t)smem ? pad : (size_t)smem, st>>>(m, a);
   return cudaGetLastError();
 }
 
@@ -581,8 +659,8 @@ static Plan make_plan(int ai, uint64_t stride, uint64_t len, uint32_t n) {
 }
 
 // Returns TH_OK if launched, 1 if this batch is not eligible (caller falls back to the bulk-copy kernel).
-// d_out_md5 != nullptr (ai == 2 only): MD5 digests as well, from the helper warp — only the assist plan can do that;
-// returns 1 for any other plan.
+// d_out_md5 != nullptr (ai == 2 only): MD5 digests as well, from the same launch (digest_parts_kernel) — only where the
+// SHA-256 plan is the chain + helper one; returns 1 for any other plan.
 static int launch_uniform(int ai, const void* d_base, uint64_t stride, uint64_t len, uint32_t n, uint8_t* d_out,
                           const uint8_t* d_expected, uint32_t* d_ok_bits, cudaStream_t st, uint8_t* d_out_md5 = nullptr) {
   const Plan pl = make_plan(ai, stride, len, n);
@@ -604,8 +682,19 @@ static int launch_uniform(int ai, const void* d_base, uint64_t stride, uint64_t 
       pad = kRoomySmem;
     }
   }
-  if (pl.path == 4 && d_out_md5) {
-    const cudaError_t e = launch_assist<Sha256, 2, 2, 4, true>(tmap, a, grid, 64, pad, st);
+  if (pl.path == 4 && d_out_md5) {  // MD5 + SHA-256 in one launch (digest_parts_kernel)
+    const uint32_t groups = (n + 31u) / 32u;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaError_t e;
+    if (groups <= (uint32_t)sms) {  // one group per CTA; `grid` is already padded to one CTA per SM and salted
+      e = g_opts.parts_trips == 4 ? launch_parts<2, 2, 4, 1, 4>(tmap, a, grid, pad, st) : launch_parts<2, 2, 4, 1, 2>(tmap, a, grid, pad, st);
+    } else {                        // two groups per CTA, one CTA per SM (its shared memory does not leave room for two)
+      a.salt = 0;
+      e = g_opts.parts_trips == 4 ? launch_parts<2, 2, 3, 2, 4>(tmap, a, (groups + 1u) / 2u, 0, st)
+                                  : launch_parts<2, 2, 3, 2, 2>(tmap, a, (groups + 1u) / 2u, 0, st);
+    }
     return e == cudaSuccess ? TH_OK : TH_ECUDA;
   }
   if (pl.path == 4) {
@@ -845,6 +934,7 @@ int th_set_option(const char* name, long long value) {
   if (k == "sliced_min_groups") { if (value < 1) return TH_EINVAL; th::g_opts.sliced_min_groups = (int)value; return TH_OK; }
   if (k == "ragged_rows") { if (value < 0 || value > 1) return TH_EINVAL; th::g_opts.ragged_rows = (int)value; return TH_OK; }
   if (k == "md5_lone") { if (value < 0 || value > 1) return TH_EINVAL; th::g_opts.md5_lone = (int)value; return TH_OK; }
+  if (k == "parts_trips") { if (value != 2 && value != 4) return TH_EINVAL; th::g_opts.parts_trips = (int)value; return TH_OK; }
   if (k == "fuse_md5_sha256") { if (value < 0 || value > 1) return TH_EINVAL; th::g_opts.fuse_md5_sha256 = (int)value; return TH_OK; }
   if (k == "rows_variant") {
     if (value < 0 || value >= th::kNumRowsVariants) return TH_EINVAL;

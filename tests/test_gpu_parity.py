@@ -215,37 +215,50 @@ def test_assist_kernel_schedule_offload(torch, L):
 
 
 @pytest.mark.parametrize("n,ln", [(1, 1024), (5, 4096 + 55), (33, 100000 + 56), (64, (1 << 20) + 63), (40, 262144), (3, 1 << 20), (7, 16 << 20)])
-def test_fused_md5_sha256_kernel_vs_hashlib(torch, L, n, ln):
-    """th_set_option("fuse_md5_sha256", 1): MD5 + SHA-256 of few large equal-length messages in ONE launch — the SHA-256
-    chain's helper warp runs the MD5 chain on the words it holds (kernels.cu, MD5_TOO).  Off by default (it measured
-    slower than the two concurrent kernels) but kept selectable, so it is kept correct.  Tail lengths
-    cover one and two padding blocks, where MD5 and SHA-256 pad differently (little- vs big-endian bit length)."""
+def test_md5_sha256_one_launch_kernel_vs_hashlib(torch, L, n, ln):
+    """th_md5_sha256_batch: MD5 + SHA-256 of few large equal-length messages in ONE launch (digest_parts_kernel: SHA-256
+    chain warp, schedule helper warp and an MD5 chain warp per group, each on a sub-partition of its own) — and, with
+    the option off, as the two separate kernels.  Tail lengths cover one and two padding blocks, where MD5 and SHA-256
+    pad differently (little- vs big-endian bit length); rows past n are zero-filled by the TMA unit."""
     stride = (ln + 15) & ~15
     rng = np.random.default_rng(n * 7919 + ln)
     host = rng.integers(0, 256, n * stride, dtype=np.uint8)
     d = torch.from_numpy(host).cuda()
     bufs = [host[i * stride:i * stride + ln] for i in range(n)]
-    assert L.th_md5_sha256_fused(stride, ln, n) == 0  # the default: two launches, one after the other on the stream
-    p5 = torch.full((n * 16,), 0xEE, dtype=torch.uint8, device="cuda")
-    p256 = torch.full((n * 32,), 0xEE, dtype=torch.uint8, device="cuda")
-    assert L.th_md5_sha256_batch(d.data_ptr(), stride, ln, n, p5.data_ptr(), p256.data_ptr(), None) == 0
-    torch.cuda.synchronize()
-    assert (p5.cpu().numpy().reshape(n, 16) == ref_digests(MD5, bufs)).all()
-    assert (p256.cpu().numpy().reshape(n, 32) == ref_digests(SHA256, bufs)).all()
-    assert L.th_set_option(b"fuse_md5_sha256", 1) == 0
     try:
-        assert L.th_md5_sha256_fused(stride, ln, n) == 1
-        o5, o256 = torch.zeros_like(p5), torch.zeros_like(p256)
-        assert L.th_md5_sha256_batch(d.data_ptr(), stride, ln, n, o5.data_ptr(), o256.data_ptr(), None) == 0
-        torch.cuda.synchronize()
-        assert torch.equal(p5, o5) and torch.equal(p256, o256)
+        for fuse in (1, 0):
+            assert L.th_set_option(b"fuse_md5_sha256", fuse) == 0
+            assert L.th_md5_sha256_fused(stride, ln, n) == fuse
+            o5 = torch.full((n * 16,), 0xEE, dtype=torch.uint8, device="cuda")
+            o256 = torch.full((n * 32,), 0xEE, dtype=torch.uint8, device="cuda")
+            assert L.th_md5_sha256_batch(d.data_ptr(), stride, ln, n, o5.data_ptr(), o256.data_ptr(), None) == 0
+            torch.cuda.synchronize()
+            assert (o5.cpu().numpy().reshape(n, 16) == ref_digests(MD5, bufs)).all(), fuse
+            assert (o256.cpu().numpy().reshape(n, 32) == ref_digests(SHA256, bufs)).all(), fuse
     finally:
-        assert L.th_set_option(b"fuse_md5_sha256", 0) == 0
+        assert L.th_set_option(b"fuse_md5_sha256", 1) == 0
 
 
-def test_submit_md5_and_sha256_of_parts_can_share_one_launch(torch, L):
-    """With the fused kernel switched on, th_submit with MD5 | SHA-256 over an object's parts (equal-length prefix +
-    short last part) launches one kernel per item — 2 instead of 4; SHA-1 of the same slot still has its own."""
+def test_md5_sha256_one_launch_kernel_two_groups_per_cta(torch, L):
+    """More groups than SMs (149..296): digest_parts_kernel runs two groups per CTA — two SHA-256 chains, their two
+    helpers and two MD5 chains in eight warp slots.  5,000 x 64 KiB-ish messages = 157 groups, the last one ragged."""
+    n, ln = 5000, 65536 + 4096 + 57
+    stride = (ln + 15) & ~15
+    host = np.random.default_rng(157).integers(0, 256, n * stride, dtype=np.uint8)
+    d = torch.from_numpy(host).cuda()
+    assert L.th_md5_sha256_fused(stride, ln, n) == 1
+    o5 = torch.zeros(n * 16, dtype=torch.uint8, device="cuda")
+    o256 = torch.zeros(n * 32, dtype=torch.uint8, device="cuda")
+    assert L.th_md5_sha256_batch(d.data_ptr(), stride, ln, n, o5.data_ptr(), o256.data_ptr(), None) == 0
+    torch.cuda.synchronize()
+    bufs = [host[i * stride:i * stride + ln] for i in range(n)]
+    assert (o5.cpu().numpy().reshape(n, 16) == ref_digests(MD5, bufs)).all()
+    assert (o256.cpu().numpy().reshape(n, 32) == ref_digests(SHA256, bufs)).all()
+
+
+def test_submit_md5_and_sha256_of_parts_share_one_launch(torch, L):
+    """th_submit with MD5 | SHA-256 over an object's parts (equal-length prefix + short last part) launches one kernel
+    per item — 2 instead of 4; SHA-1 of the same slot still has its own.  With the option off: 4."""
     from downloader_b200 import Engine
     part, last = 4 << 20, (1 << 20) + 12345
     nparts = 6
@@ -255,35 +268,35 @@ def test_submit_md5_and_sha256_of_parts_can_share_one_launch(torch, L):
     offs = np.arange(nparts, dtype=np.uint64) * part
     lens = np.array([part] * (nparts - 1) + [last], np.uint64)
     bufs = [data[int(o):int(o + l)] for o, l in zip(offs, lens)]
-    assert L.th_set_option(b"fuse_md5_sha256", 1) == 0
-    try:
-        with Engine([0], ring_bytes=64 << 20) as e:
-            e.set_timing(True)
-            slot, view = e.ring_acquire(total)
-            view[:] = data
-            s0 = e.stats()
-            t = e.submit(slot, offs, lens, MD5 | SHA256)
-            tm = e.timing(t)
-            r = e.result(t, nparts, MD5 | SHA256)
-            s1 = e.stats()
-            assert (r[MD5] == ref_digests(MD5, bufs)).all() and (r[SHA256] == ref_digests(SHA256, bufs)).all()
-            assert s1["launches"] - s0["launches"] == 2
-            assert tm[3] >= 0 and tm[4] > tm[3] and tm[6] > tm[5]  # the MD5 timeline is the fused launches'
-            slot, view = e.ring_acquire(total)
-            view[:] = data
-            t = e.submit(slot, offs, lens, SHA1 | MD5 | SHA256)
-            r = e.result(t, nparts, SHA1 | MD5 | SHA256)
-            assert (r[SHA1] == ref_digests(SHA1, bufs)).all() and (r[MD5] == ref_digests(MD5, bufs)).all()
-            assert e.stats()["launches"] - s1["launches"] == 4
-    finally:
-        assert L.th_set_option(b"fuse_md5_sha256", 0) == 0
-    with Engine([0], ring_bytes=64 << 20) as e:  # the default: separate MD5 and SHA-256 kernels on separate streams
+    with Engine([0], ring_bytes=64 << 20) as e:
+        e.set_timing(True)
         slot, view = e.ring_acquire(total)
         view[:] = data
         s0 = e.stats()
-        r = e.result(e.submit(slot, offs, lens, MD5 | SHA256), nparts, MD5 | SHA256)
+        t = e.submit(slot, offs, lens, MD5 | SHA256)
+        tm = e.timing(t)
+        r = e.result(t, nparts, MD5 | SHA256)
+        s1 = e.stats()
         assert (r[MD5] == ref_digests(MD5, bufs)).all() and (r[SHA256] == ref_digests(SHA256, bufs)).all()
-        assert e.stats()["launches"] - s0["launches"] == 4
+        assert s1["launches"] - s0["launches"] == 2
+        assert tm[3] >= 0 and tm[4] > tm[3] and tm[6] > tm[5]  # the MD5 timeline is the shared launches'
+        slot, view = e.ring_acquire(total)
+        view[:] = data
+        t = e.submit(slot, offs, lens, SHA1 | MD5 | SHA256)
+        r = e.result(t, nparts, SHA1 | MD5 | SHA256)
+        assert (r[SHA1] == ref_digests(SHA1, bufs)).all() and (r[MD5] == ref_digests(MD5, bufs)).all()
+        assert e.stats()["launches"] - s1["launches"] == 4
+    assert L.th_set_option(b"fuse_md5_sha256", 0) == 0
+    try:
+        with Engine([0], ring_bytes=64 << 20) as e:  # separate MD5 and SHA-256 kernels on separate streams
+            slot, view = e.ring_acquire(total)
+            view[:] = data
+            s0 = e.stats()
+            r = e.result(e.submit(slot, offs, lens, MD5 | SHA256), nparts, MD5 | SHA256)
+            assert (r[MD5] == ref_digests(MD5, bufs)).all() and (r[SHA256] == ref_digests(SHA256, bufs)).all()
+            assert e.stats()["launches"] - s0["launches"] == 4
+    finally:
+        assert L.th_set_option(b"fuse_md5_sha256", 1) == 0
 
 
 def test_sliced_kernel_time_slicing_engaged(torch, L):
@@ -597,7 +610,7 @@ def test_few_large_ragged_messages_take_lone_launches(eng):
     s1 = eng.stats()
     for a in (SHA1, MD5, SHA256):
         assert (out[a] == ref_digests(a, bufs)).all(), NAMES[a]
-    assert s1["launches"] - s0["launches"] == 3 * len(lens)  # one launch per message and digest
+    assert s1["launches"] - s0["launches"] == 2 * len(lens)  # per message: SHA-1, and one launch for MD5 + SHA-256
     exp = ref_digests(SHA1, bufs).copy()
     exp[2, 0] ^= 1
     out = eng.hash_batch(bufs, SHA1 | MD5, expected_sha1=exp)
@@ -762,7 +775,7 @@ def test_heavy_tailed_batch_peels_outliers_into_lone_launches(eng):
     for a in (SHA1, MD5, SHA256):
         wrong = np.nonzero((out[a] != ref_digests(a, bufs)).any(axis=1))[0]
         assert wrong.size == 0, (NAMES[a], [lens[i] for i in wrong[:5]])
-    assert s1["launches"] - s0["launches"] == 3 * (1 + len(big))
+    assert s1["launches"] - s0["launches"] == 3 + 2 * len(big)  # per-lane remainder x 3 digests; each outlier: SHA-1 + one MD5/SHA-256 launch
     # with a verify table the remainder stays one launch (the bitfield word is written by one ballot)
     exp = ref_digests(SHA1, bufs).copy()
     exp[40, 3] ^= 0x10

@@ -29,8 +29,15 @@ def main():
     ap.add_argument("--only", default="", help="one of sha1, md5, sha256, md5+sha256")
     ap.add_argument("--iters", type=int, default=2)
     ap.add_argument("--no-verify", action="store_true")
+    ap.add_argument("--opt", action="append", default=[], help="th_set_option name=value (tuning), e.g. parts_trips=4")
+    ap.add_argument("--no-fuse", action="store_true", help="MD5 + SHA-256 as two kernels on two streams instead of the one-launch kernel")
     a = ap.parse_args()
     L = _capi.lib()
+    if a.no_fuse:
+        assert L.th_set_option(b"fuse_md5_sha256", 0) == 0
+    for o in a.opt:
+        k, v = o.split("=")
+        assert L.th_set_option(k.encode(), int(v)) == 0, o
     n, ln = a.parts, a.mib << 20
     data = torch.empty(n * ln, dtype=torch.uint8, device="cuda")
     L.th_synth_fill(data.data_ptr(), 0, n, ln, ln, 5, None)
@@ -55,10 +62,14 @@ def main():
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(cur)
             side.wait_stream(cur)
-            assert launch(algs[0], cur) == 0
-            if len(algs) > 1:
-                assert launch(algs[1], side) == 0
-                cur.wait_stream(side)
+            if len(algs) > 1 and L.th_md5_sha256_fused(ln, ln, n) == 1:  # one launch does both (digest_parts_kernel)
+                assert L.th_md5_sha256_batch(data.data_ptr(), ln, ln, n, outs["md5"].data_ptr(), outs["sha256"].data_ptr(),
+                                             C.c_void_p(cur.cuda_stream)) == 0
+            else:
+                assert launch(algs[0], cur) == 0
+                if len(algs) > 1:
+                    assert launch(algs[1], side) == 0
+                    cur.wait_stream(side)
             e1.record(cur)
             torch.cuda.synchronize()
             ms = e0.elapsed_time(e1)
@@ -73,7 +84,8 @@ def main():
         gbps = n * ln / best / 1e6
         print(json.dumps({"algs": "+".join(algs), "parts": n, "part_MiB": a.mib, "GiB": n * ln >> 30, "ms": round(best, 1),
                           "GBps": round(gbps, 1), "int_roofline_GBps": round(roof, 1), "frac": round(gbps / roof, 3),
-                          "kernel": _capi.plan({"sha1": 1, "md5": 2, "sha256": 4}[algs[-1]], ln, ln, n).split(":")[0],
+                          "kernel": ("parts (one launch)" if len(algs) > 1 and L.th_md5_sha256_fused(ln, ln, n) == 1 else
+                                     _capi.plan({"sha1": 1, "md5": 2, "sha256": 4}[algs[-1]], ln, ln, n).split(":")[0]),
                           "verified": f"{len(pick)} of {n} vs hashlib"}), flush=True)
 
 

@@ -72,7 +72,7 @@ __global__ void md5_step_k(uint32_t* out, uint32_t one, uint32_t seed, long long
 // MODE 0 md5 compress, 1 sha1 compress, 2 sha256 compress (message words in registers, made opaque every block);
 // 10+V sha1 chain-warp rounds variant V, 20+V sha256 chain-warp rounds variant V (pre-expanded W+K read from shared
 // memory with LDS.128); 30 sha1 helper expansion, 40+V sha256 helper expansion variant V (written to shared memory),
-// 50+V the same with the MD5 chain of the block interleaved (the fused MD5 + SHA-256 helper)
+// 50+V the same after an MD5 compression of the block (one warp doing both: the two costs simply add up)
 template <int MODE>
 __global__ void compress_k(uint32_t* out, uint32_t one, uint32_t seed, long long* cyc) {
   __shared__ uint4 ring[80 * 32];
@@ -96,26 +96,21 @@ __global__ void compress_k(uint32_t* out, uint32_t one, uint32_t seed, long long
     if (MODE == 1) { uint32_t v[16]; for (int i = 0; i < 16; i++) v[i] = w[i]; Sha1::compress(h, v, one); }
     if (MODE == 2) { uint32_t v[16]; for (int i = 0; i < 16; i++) v[i] = w[i]; Sha256::compress(h, v, one); }
     if (MODE >= 10 && MODE < 20) Assist<Sha1>::rounds<MODE - 10, 80>(h, ring + lane, one);
-    if (MODE >= 20 && MODE < 30) Assist<Sha256>::rounds<MODE - 20, 64>(h, ring + lane, one);
+    if (MODE >= 20 && MODE < 30) Assist<Sha256>::rounds<MODE - 20, 64, 1>(h, ring + lane, one);
+    if (MODE >= 220 && MODE < 230) Assist<Sha256>::rounds<MODE - 220, 64, 4>(h, ring + lane, one);  // 4 trips of 16 rounds
+    if (MODE >= 320 && MODE < 330) Assist<Sha256>::rounds<MODE - 320, 64, 2>(h, ring + lane, one);  // 2 trips of 32 rounds
     if (MODE >= 110 && MODE < 120) Assist<Sha1>::rounds<MODE - 110, 0>(h, ring + lane, one);   // + K in the chain warp
-    if (MODE >= 120 && MODE < 130) Assist<Sha256>::rounds<MODE - 120, 0>(h, ring + lane, one);
+    if (MODE >= 120 && MODE < 130) Assist<Sha256>::rounds<MODE - 120, 0, 1>(h, ring + lane, one);
     // (the expanded window is fed back into w[0]: without a loop-carried value the compiler hoists the whole expansion)
     if (MODE == 30) { uint32_t v[16]; for (int i = 0; i < 16; i++) v[i] = bswap(w[i]); Assist<Sha1>::expand<80>(v, dst, one); w[0] += v[15]; }
     if (MODE == 130) { uint32_t v[16]; for (int i = 0; i < 16; i++) v[i] = bswap(w[i]); Assist<Sha1>::expand<0>(v, dst, one); w[0] += v[15]; }
     if (MODE >= 140 && MODE < 150) { uint32_t v[16]; for (int i = 0; i < 16; i++) v[i] = bswap(w[i]); Assist<Sha256>::expand<MODE - 140, 0>(v, dst, one); w[0] += v[15]; }
-    if (MODE >= 160 && MODE < 170) { uint32_t v[16]; for (int i = 0; i < 16; i++) v[i] = bswap(w[i]); expand_sha256_with_md5<MODE - 160, 0>(v, w, h, dst, one); w[0] += v[15]; }
     if (MODE >= 40 && MODE < 50) { uint32_t v[16]; for (int i = 0; i < 16; i++) v[i] = bswap(w[i]); Assist<Sha256>::expand<MODE - 40, 64>(v, dst, one); w[0] += v[15]; }
     if (MODE >= 50 && MODE < 60) {  // MD5 block, then the expansion, as two calls (ptxas is left to interleave them)
       uint32_t v[16];
       for (int i = 0; i < 16; i++) v[i] = bswap(w[i]);
       Md5::compress(h, w, one);
       Assist<Sha256>::expand<MODE - 50, 64>(v, dst, one);
-      w[0] += v[15];
-    }
-    if (MODE >= 60 && MODE < 70) {  // schedule word t / MD5 step t alternately in source order (what the kernel uses)
-      uint32_t v[16];
-      for (int i = 0; i < 16; i++) v[i] = bswap(w[i]);
-      expand_sha256_with_md5<MODE - 60, 64>(v, w, h, dst, one);
       w[0] += v[15];
     }
   }
@@ -166,18 +161,18 @@ int main() {
     printf("Assist<Sha256>::rounds<2>   %.1f (10 ALU + 8 FMA)\n", run(compress_k<22>, shapes[s]) / NBLK);
     printf("Assist<Sha256>::rounds<3>   %.1f (10 ALU + 6 FMA)\n", run(compress_k<23>, shapes[s]) / NBLK);
     printf("Assist<Sha256>::rounds<4>   %.1f (11 ALU + 4 FMA)\n", run(compress_k<24>, shapes[s]) / NBLK);
+    printf("Assist<Sha256>::rounds<1> as 4 trips of 16 rounds (4.5 KB of code)  %.1f   as 2 trips of 32 (8.7 KB)  %.1f\n",
+           run(compress_k<221>, shapes[s]) / NBLK, run(compress_k<321>, shapes[s]) / NBLK);
     printf("Assist<Sha1>::expand        %.1f cycles per block (helper warp)\n", run(compress_k<30>, shapes[s]) / NBLK);
     printf("Assist<Sha256>::expand<0>   %.1f (adds on the ALU pipe)\n", run(compress_k<40>, shapes[s]) / NBLK);
     printf("Assist<Sha256>::expand<1>   %.1f (adds as IMAD)\n", run(compress_k<41>, shapes[s]) / NBLK);
-    printf("expand<0> + Md5::compress   %.1f (the fused MD5 + SHA-256 helper)\n", run(compress_k<50>, shapes[s]) / NBLK);
+    printf("expand<0> + Md5::compress   %.1f (one warp doing both)\n", run(compress_k<50>, shapes[s]) / NBLK);
     printf("expand<1> + Md5::compress   %.1f\n", run(compress_k<51>, shapes[s]) / NBLK);
-    printf("expand_sha256_with_md5<0>   %.1f (interleaved in source order)\n", run(compress_k<60>, shapes[s]) / NBLK);
-    printf("expand_sha256_with_md5<1>   %.1f\n", run(compress_k<61>, shapes[s]) / NBLK);
     printf("-- round constants added by the chain warp instead of the helper:\n");
     printf("Assist<Sha1>::rounds<0,K>   %.1f   rounds<1,K> %.1f   expand<K> %.1f\n", run(compress_k<110>, shapes[s]) / NBLK, run(compress_k<111>, shapes[s]) / NBLK, run(compress_k<130>, shapes[s]) / NBLK);
-    printf("Assist<Sha256>::rounds<0,K> %.1f   <1,K> %.1f   <4,K> %.1f   expand<0,K> %.1f   expand<1,K> %.1f   with_md5<0,K> %.1f\n",
+    printf("Assist<Sha256>::rounds<0,K> %.1f   <1,K> %.1f   <4,K> %.1f   expand<0,K> %.1f   expand<1,K> %.1f\n",
            run(compress_k<120>, shapes[s]) / NBLK, run(compress_k<121>, shapes[s]) / NBLK, run(compress_k<124>, shapes[s]) / NBLK,
-           run(compress_k<140>, shapes[s]) / NBLK, run(compress_k<141>, shapes[s]) / NBLK, run(compress_k<160>, shapes[s]) / NBLK);
+           run(compress_k<140>, shapes[s]) / NBLK, run(compress_k<141>, shapes[s]) / NBLK);
   }
   return 0;
 }
