@@ -573,7 +573,9 @@ def run_workload(E, args, name, algs, n, ln, desc, first_msg, steps, warmup, do_
             else f"flags exactly the {len(corrupt)} corrupted of {n}"
     entry["verified_vs_oracle"] = report
     if do_e2e:
-        entry["e2e"] = e2e_leg(E, args, data, n, ln, names, got, exp_host, corrupt, max(1, min(steps, 5)), warmup)
+        # 5 streamed steps whatever `steps` is: the last step's chains drain after the last copy, and with 16 MiB parts
+        # that tail (one chain latency, 0.24 s) is most of a step — over 3 steps it alone costs 20 % of the figure
+        entry["e2e"] = e2e_leg(E, args, data, n, ln, names, got, exp_host, corrupt, max(1, min(args.steps, 5)), warmup)
     if own:
         del data
     del outs, expected, ok
