@@ -180,6 +180,9 @@ __device__ __forceinline__ void mbar_init_fence() {
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   asm volatile(
       "{\n"
@@ -850,10 +853,15 @@ struct Assist<Sha1> {
 // Helper warp: streams the group's message through the TMA tiles (as tile_segment does) and, instead of
 // compressing, expands every block (padding blocks included) into schedule-ring slot (block % SS).
 // bar0: first of the 2*SS named barriers this chain / helper pair hands slots over with (a CTA may hold two pairs).
-template <class A, int K, int NST, int SS>
+// BPS: blocks per ring slot — a slot is handed over when it holds BPS expanded blocks (or the message's last one), so
+// the two bar.sync / bar.arrive a hand-over costs each warp are paid once per BPS blocks.
+// SHARED: the tiles belong to another warp (tile_consume_shared<..., ISSUER>), which issues the TMA loads; this warp only
+// waits for a stage's `full` mbarrier and, when it is done with the stage, arrives on its `empty` mbarrier (s_empty).
+// The helper is the warp with the least slack of the MD5 + SHA-256 trio, so it is spared the issuing.
+template <class A, int K, int NST, int SS, int BPS = 1, bool SHARED = false>
 __device__ __forceinline__ void assist_produce(const void* tmap, uint32_t row0, uint64_t len, uint32_t nch,
                                                uint32_t s_tiles, uint32_t s_bar, uint32_t s_ring, int lane,
-                                               uint32_t one, int bar0 = 1) {
+                                               uint32_t one, int bar0 = 1, uint32_t s_empty = 0) {
   using G = Tiles<K, NST>;
   constexpr int CH = G::CH;
   constexpr uint32_t SLOT = Assist<A>::WPB * 128;
@@ -869,12 +877,14 @@ __device__ __forceinline__ void assist_produce(const void* tmap, uint32_t row0, 
         if ((uint32_t)j < ntile) tma_tile_2d(s_tiles + (s * K + j) * G::TILE, tmap, (uint32_t)pos + 128u * j, row0, bar);
     }
   };
+  if (!SHARED) {
 #pragma unroll
-  for (int i = 0; i < NST; i++)
-    if ((uint32_t)i < nch) issue((uint32_t)i, i);
+    for (int i = 0; i < NST; i++)
+      if ((uint32_t)i < nch) issue((uint32_t)i, i);
+  }
   const uint32_t swz = (uint32_t)(lane & 7);
-  int stage = 0, slot = 0;
-  uint32_t phase = 0, produced = 0;
+  int stage = 0, slot = 0, inslot = 0;
+  uint32_t phase = 0, produced = 0;  // produced: slots handed over so far
   for (uint32_t c = 0; c < nch; c++) {
     mbar_wait(s_bar + 8 * stage, (phase >> stage) & 1u);
     phase ^= 1u << stage;
@@ -896,31 +906,112 @@ __device__ __forceinline__ void assist_produce(const void* tmap, uint32_t row0, 
       if (b >= nb) pad_block<A>(w, b - nb, r, len);
 #pragma unroll
       for (int i = 0; i < 16; i++) w[i] = bswap(w[i]);
-      if (produced >= (uint32_t)SS) nb_sync(bar0 + SS + slot);  // wait until the chain warp has drained this slot
-      Assist<A>::expand(w, s_ring + slot * SLOT + lane * 16, one);
-      nb_arrive(bar0 + slot);
-      produced++;
-      if (++slot == SS) slot = 0;
+      if (inslot == 0 && produced >= (uint32_t)SS) nb_sync(bar0 + SS + slot);  // wait until the chain warp has drained this slot
+      Assist<A>::expand(w, s_ring + (slot * BPS + inslot) * SLOT + lane * 16, one);
+      if (++inslot == BPS || (last && b == nblk - 1u)) {  // slot full, or the message's last block: hand it over
+        nb_arrive(bar0 + slot);
+        produced++;
+        inslot = 0;
+        if (++slot == SS) slot = 0;
+      }
     }
     __syncwarp();
     fence_proxy_async_smem();
-    if (c + NST < nch) issue(c + NST, stage);
+    if (c + NST < nch) {
+      if (SHARED) { if (lane == 0) mbar_arrive(s_empty + 8 * stage); }
+      else issue(c + NST, stage);
+    }
+    if (++stage == NST) stage = 0;
+  }
+}
+
+// The warp that owns the tiles of the one-launch MD5 + SHA-256 kernel: it issues the TMA loads, compresses every block
+// of the group's messages with digest A (MD5) as the stages fill, and refills a stage once it AND the second reader of
+// the tiles (assist_produce<..., SHARED>, the SHA-256 helper) have arrived on the stage's `empty` mbarrier (count 2) —
+// so the parts are read from HBM once.  The MD5 chain needs half the time per block the SHA-256 pair does, so this
+// warp has the slack for the issuing and the waiting.
+template <class A, int K, int NST>
+__device__ __forceinline__ void tile_consume_shared(const void* tmap, uint32_t row0, uint64_t len, uint32_t nch, uint32_t* h,
+                                                    uint32_t s_tiles, uint32_t s_full, uint32_t s_empty, int lane, uint32_t one) {
+  using G = Tiles<K, NST>;
+  constexpr int CH = G::CH;
+  auto issue = [&](uint32_t c, int s) {
+    if (lane == 0) {
+      const uint64_t pos = (uint64_t)c * CH;
+      const uint64_t left = pos < len ? len - pos : 0;
+      const uint32_t ntile = left >= (uint64_t)CH ? (uint32_t)K : (uint32_t)((left + 127) >> 7);
+      const uint32_t bar = s_full + 8 * s;
+      mbar_arrive_expect_tx(bar, ntile * G::TILE);
+#pragma unroll
+      for (int j = 0; j < K; j++)
+        if ((uint32_t)j < ntile) tma_tile_2d(s_tiles + (s * K + j) * G::TILE, tmap, (uint32_t)pos + 128u * j, row0, bar);
+    }
+  };
+#pragma unroll
+  for (int i = 0; i < NST; i++)
+    if ((uint32_t)i < nch) issue((uint32_t)i, i);
+  const uint32_t swz = (uint32_t)(lane & 7);
+  int stage = 0;
+  uint32_t phase = 0, ephase = 0;
+  for (uint32_t c = 0; c < nch; c++) {
+    mbar_wait(s_full + 8 * stage, (phase >> stage) & 1u);
+    phase ^= 1u << stage;
+    const bool last = c == nch - 1u;
+    const uint32_t bytes = last ? (uint32_t)(len - (uint64_t)c * CH) : (uint32_t)CH;
+    const uint32_t nb = bytes >> 6, r = bytes & 63u;
+    const uint32_t nblk = nb + (last ? (r < 56 ? 1u : 2u) : 0u);
+    const uint32_t lane_base = s_tiles + stage * G::STAGE_BYTES + lane * 128;
+#pragma unroll 1
+    for (uint32_t b = 0; b < nblk; b++) {
+      uint32_t w[16];
+      const uint32_t bb = b < (uint32_t)(2 * K) ? b : 0u;  // padding block 1 past the stage: nothing to read
+      const uint32_t a = lane_base + (bb >> 1) * G::TILE;
+      const uint32_t q0 = (bb & 1u) * 4u;
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        uint4 v = lds128(a + (((q0 + q) ^ swz) << 4));
+        w[4 * q] = v.x; w[4 * q + 1] = v.y; w[4 * q + 2] = v.z; w[4 * q + 3] = v.w;
+      }
+      if (b >= nb) pad_block<A>(w, b - nb, r, len);
+      if (A::BE) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) w[i] = bswap(w[i]);
+      }
+      A::compress(h, w, one);
+    }
+    __syncwarp();
+    fence_proxy_async_smem();
+    if (c + NST < nch) {
+      if (lane == 0) {
+        mbar_arrive(s_empty + 8 * stage);
+        mbar_wait(s_empty + 8 * stage, (ephase >> stage) & 1u);  // the other reader is done with this stage too
+      }
+      ephase ^= 1u << stage;
+      issue(c + NST, stage);
+    }
     if (++stage == NST) stage = 0;
   }
 }
 
 // Chain warp: consumes `total` expanded blocks.
-template <class A, int SS, int TRIPS = 1>
+template <class A, int SS, int TRIPS = 1, int BPS = 1>
 __device__ __forceinline__ void assist_consume(uint32_t total, uint32_t* h, const unsigned char* ring, int lane,
                                                uint32_t one, int bar0 = 1) {
   constexpr uint32_t SLOT = Assist<A>::WPB * 128;
+  const uint32_t nslots = (total + BPS - 1) / BPS;
   int slot = 0;
-#pragma unroll 1  // one copy of the rounds: two would not fit the 32 KB instruction cache beside the helper's loop
-  for (uint32_t i = 0; i < total; i++) {
+  uint32_t done = 0;
+  for (uint32_t i = 0; i < nslots; i++) {
     nb_sync(bar0 + slot);
-    if constexpr (TRIPS == 1) Assist<A>::rounds(h, reinterpret_cast<const uint4*>(ring + slot * SLOT) + lane, one);
-    else Assist<A>::template rounds<1, Assist<A>::KH, TRIPS>(h, reinterpret_cast<const uint4*>(ring + slot * SLOT) + lane, one);
-    if (i + SS < total) nb_arrive(bar0 + SS + slot);  // hand the slot back (only if the helper will reuse it)
+    const uint32_t nb = total - done < (uint32_t)BPS ? total - done : (uint32_t)BPS;
+#pragma unroll 1  // one copy of the rounds: two would not fit the 32 KB instruction cache beside the helper's loop
+    for (uint32_t j = 0; j < nb; j++) {
+      const uint4* src = reinterpret_cast<const uint4*>(ring + (slot * BPS + j) * SLOT) + lane;
+      if constexpr (TRIPS == 1) Assist<A>::rounds(h, src, one);
+      else Assist<A>::template rounds<1, Assist<A>::KH, TRIPS>(h, src, one);
+    }
+    done += nb;
+    if (i + SS < nslots) nb_arrive(bar0 + SS + slot);  // hand the slot back (only if the helper will reuse it)
     if (++slot == SS) slot = 0;
   }
 }

@@ -175,7 +175,8 @@ __global__ void __launch_bounds__(32) digest_tile_kernel(const __grid_constant__
 }
 
 // Few, large messages (fewer groups than SM sub-partitions): chain warp + schedule helper warp per group.
-template <class A, int K, int NST, int SS>
+// SS ring slots of BPS expanded blocks each.
+template <class A, int K, int NST, int SS, int BPS = 1>
 __global__ void __launch_bounds__(64) digest_assist_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs p) {
   extern __shared__ __align__(1024) unsigned char smem[];
   using G = Tiles<K, NST>;
@@ -184,7 +185,7 @@ __global__ void __launch_bounds__(64) digest_assist_kernel(const __grid_constant
   if (!spread_group(p, &group)) return;
   const uint32_t s_tiles = smem_u32(smem);
   const uint32_t s_ring = s_tiles + G::WARP_BYTES;
-  const uint32_t s_bar = s_ring + SS * Assist<A>::WPB * 128;
+  const uint32_t s_bar = s_ring + SS * BPS * Assist<A>::WPB * 128;
   if (threadIdx.x == 32) {
     prefetch_tmap(&tmap);
 #pragma unroll
@@ -196,34 +197,33 @@ __global__ void __launch_bounds__(64) digest_assist_kernel(const __grid_constant
   const uint32_t r = (uint32_t)(p.len & 63u);
   const uint32_t total = (uint32_t)(p.len >> 6) + (r < 56 ? 1u : 2u);
   if (warp == 1) {
-    assist_produce<A, K, NST, SS>(&tmap, group * 32u, p.len, nch, s_tiles, s_bar, s_ring, lane, p.one);
+    assist_produce<A, K, NST, SS, BPS>(&tmap, group * 32u, p.len, nch, s_tiles, s_bar, s_ring, lane, p.one);
   } else {
     uint32_t h[A::NS];
     A::init(h);
-    assist_consume<A, SS>(total, h, smem + G::WARP_BYTES, lane, p.one);
+    assist_consume<A, SS, 1, BPS>(total, h, smem + G::WARP_BYTES, lane, p.one);
     finish_group<A>(p, group, lane, h);
   }
 }
 
 // MD5 AND SHA-256 of few large messages — the digests an S3 part needs (lib/upload.js:45 -> [dep] minio getHashSummer)
-// — in ONE launch whose CTAs place every chain on a sub-partition of its own.  Launched as two kernels, the MD5 warps
-// land wherever the block scheduler puts them: next to a SHA-256 chain warp (which needs every ALU slot of its
-// sub-partition) as often as next to a helper warp or on an idle sub-partition — 4,096 x 16 MiB parts measured anything
-// from 246 to 294 ms from run to run and launch order to launch order, against 227 ms for SHA-256 alone.  Warps of one
-// CTA are dealt to the four sub-partitions in order, so here the roles are fixed by warp index:
+// — in ONE launch that reads the parts once and fixes which sub-partition every warp runs on.  Launched as two kernels
+// (MD5 tile kernel + SHA-256 chain/helper kernel) config 3 took 246..294 ms from run to run against 227 ms for SHA-256
+// alone, and read every part twice.  Warps of one CTA are dealt to the four sub-partitions in order, so the roles are
+// fixed by warp index:
 //   GP = 1 (up to one group per SM):  warp 0 SHA-256 chain, 1 schedule helper, 2 MD5 chain            (3 sub-partitions)
 //   GP = 2 (up to two groups per SM): warps 0,1 the two SHA-256 chains, 2,3 their helpers, 4,5 exit at once,
 //                                     6,7 the two MD5 chains — which share sub-partitions 2,3 with the helpers, the
 //                                     warps with issue slots to spare, never with a chain warp.
-// The MD5 warp streams the parts through its own tiles (tile_stream_lone); it reads the same bytes a moment after or
-// before the helper does, so the second read is served by L2 (dram__bytes_read stays at the message bytes).
-template <int K, int NST, int SS, int GP, int TRIPS>
+// The MD5 warp owns the tiles and issues the TMA loads (tile_consume_shared); the helper reads the same tiles: both wait
+// on a stage's `full` mbarrier, and the stage is refilled only after both have arrived on its `empty` mbarrier.  The SHA-256 rounds run as TRIPS trips so
+// that chain loop + helper loop + MD5 loop fit the 32 KB instruction cache (see Assist<Sha256>::rounds).
+template <int K, int NST, int SS, int BPS, int GP, int TRIPS>
 __global__ void __launch_bounds__(GP == 1 ? 96 : 256) digest_parts_kernel(const __grid_constant__ CUtensorMap tmap, const TileArgs p) {
   extern __shared__ __align__(1024) unsigned char smem[];
   using G = Tiles<K, NST>;
-  using GM = Tiles<4, 3>;  // the MD5 warp's own ring (tile_stream_lone wants three stages)
-  constexpr uint32_t RING_BYTES = SS * Assist<Sha256>::WPB * 128;
-  constexpr uint32_t PER_GROUP = G::WARP_BYTES + RING_BYTES + GM::WARP_BYTES;
+  constexpr uint32_t RING_BYTES = SS * BPS * Assist<Sha256>::WPB * 128;
+  constexpr uint32_t PER_GROUP = G::WARP_BYTES + RING_BYTES;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   // role and which of the CTA's groups this warp serves
   int role, g;  // role 0 chain, 1 helper, 2 md5, 3 none
@@ -241,16 +241,14 @@ __global__ void __launch_bounds__(GP == 1 ? 96 : 256) digest_parts_kernel(const 
   unsigned char* base = smem + (size_t)g * PER_GROUP;
   const uint32_t s_tiles = smem_u32(base);
   const uint32_t s_ring = s_tiles + G::WARP_BYTES;
-  const uint32_t s_md5 = s_ring + RING_BYTES;
-  const uint32_t s_bar = smem_u32(smem) + GP * PER_GROUP + (uint32_t)g * 64u;  // per group: NST helper + 3 MD5 mbarriers
-  if (active && lane == 0 && role != 0) {
-    if (role == 1) {
-      prefetch_tmap(&tmap);
+  const uint32_t s_full = smem_u32(smem) + GP * PER_GROUP + (uint32_t)g * 64u;  // per group: NST full + NST empty mbarriers
+  const uint32_t s_empty = s_full + 8 * NST;
+  if (active && lane == 0 && role == 2) {
+    prefetch_tmap(&tmap);
 #pragma unroll
-      for (int s = 0; s < NST; s++) mbar_init(s_bar + 8 * s, 1);
-    } else {
-#pragma unroll
-      for (int s = 0; s < 3; s++) mbar_init(s_bar + 32 + 8 * s, 1);
+    for (int s = 0; s < NST; s++) {
+      mbar_init(s_full + 8 * s, 1);
+      mbar_init(s_empty + 8 * s, 2);  // helper + MD5 warp
     }
     mbar_init_fence();
   }
@@ -258,18 +256,19 @@ __global__ void __launch_bounds__(GP == 1 ? 96 : 256) digest_parts_kernel(const 
   if (!active) return;
   const uint32_t r = (uint32_t)(p.len & 63u);
   const uint32_t total = (uint32_t)(p.len >> 6) + (r < 56 ? 1u : 2u);
+  const uint32_t nch = (uint32_t)(p.len / G::CH) + 1u;
   const int bar0 = 1 + g * 2 * SS;
   if (role == 1) {
-    assist_produce<Sha256, K, NST, SS>(&tmap, group * 32u, p.len, (uint32_t)(p.len / G::CH) + 1u, s_tiles, s_bar, s_ring, lane, p.one, bar0);
+    assist_produce<Sha256, K, NST, SS, BPS, true>(&tmap, group * 32u, p.len, nch, s_tiles, s_full, s_ring, lane, p.one, bar0, s_empty);
   } else if (role == 0) {
     uint32_t h[Sha256::NS];
     Sha256::init(h);
-    assist_consume<Sha256, SS, TRIPS>(total, h, base + G::WARP_BYTES, lane, p.one, bar0);  // rolled rounds: see Assist<Sha256>::rounds
+    assist_consume<Sha256, SS, TRIPS, BPS>(total, h, base + G::WARP_BYTES, lane, p.one, bar0);  // rolled rounds: see Assist<Sha256>::rounds
     finish_group<Sha256>(p, group, lane, h);
   } else {
     uint32_t h[Md5::NS];
     Md5::init(h);
-    tile_stream_lone<Md5, 4, 3>(&tmap, group * 32u, p.len, (uint32_t)(p.len / GM::CH) + 1u, h, s_md5, s_bar + 32, lane, p.one);
+    tile_consume_shared<Md5, K, NST>(&tmap, group * 32u, p.len, nch, h, s_tiles, s_full, s_empty, lane, p.one);
     const uint32_t idx = group * 32u + lane;
     if (idx < p.n) store_digest<Md5>(p.out_md5 + (size_t)idx * Md5::DLEN, h);
   }
@@ -557,27 +556,28 @@ cudaError_t launch_sliced(const CUtensorMap& m, const TileArgs& a, uint32_t grid
   return cudaGetLastError();
 }
 
-template <class A, int K, int NST, int SS>
+template <class A, int K, int NST, int SS, int BPS = 1>
 cudaError_t launch_assist(const CUtensorMap& m, const TileArgs& a, uint32_t grid, uint32_t, size_t pad, cudaStream_t st) {
-  constexpr int smem = Tiles<K, NST>::WARP_BYTES + SS * Assist<A>::WPB * 128 + 8 * NST;
+  constexpr int smem = Tiles<K, NST>::WARP_BYTES + SS * BPS * Assist<A>::WPB * 128 + 8 * NST;
   static bool done[64] = {};
-  cudaError_t e0 = allow_smem(digest_assist_kernel<A, K, NST, SS>, done, smem > kRoomySmem ? smem : kRoomySmem);
+  cudaError_t e0 = allow_smem(digest_assist_kernel<A, K, NST, SS, BPS>, done, smem > kRoomySmem ? smem : kRoomySmem);
   if (e0 != cudaSuccess) return e0;
-  digest_assist_kernel<A, K, NST, SS><<<grid, 64, pad > (size_t)smem ? pad : (size_t)smem, st>>>(m, a);
+  digest_assist_kernel<A, K, NST, SS, BPS><<<grid, 64, pad > (size_t)smem ? pad : (size_t)smem, st>>>(m, a);
   return cudaGetLastError();
 }
 
-template <int K, int NST, int SS, int GP>
-constexpr int parts_smem() { return GP * (Tiles<K, NST>::WARP_BYTES + SS * Assist<Sha256>::WPB * 128 + Tiles<4, 3>::WARP_BYTES) + GP * 64; }
+template <int K, int NST, int SS, int BPS, int GP>
+constexpr int parts_smem() { return GP * (Tiles<K, NST>::WARP_BYTES + SS * BPS * Assist<Sha256>::WPB * 128) + GP * 64; }
 
-template <int K, int NST, int SS, int GP, int TRIPS>
+template <int K, int NST, int SS, int BPS, int GP, int TRIPS>
 cudaError_t launch_parts(const CUtensorMap& m, const TileArgs& a, uint32_t grid, size_t pad, cudaStream_t st) {
-  constexpr int smem = parts_smem<K, NST, SS, GP>();
+  constexpr int smem = parts_smem<K, NST, SS, BPS, GP>();
   static_assert(smem <= 227 * 1024, "digest_parts_kernel: shared memory");
+  static_assert(GP * 2 * SS <= 15, "named barriers 1..15");
   static bool done[64] = {};
-  cudaError_t e0 = allow_smem(digest_parts_kernel<K, NST, SS, GP, TRIPS>, done, smem > kRoomySmem ? smem : kRoomySmem);
+  cudaError_t e0 = allow_smem(digest_parts_kernel<K, NST, SS, BPS, GP, TRIPS>, done, smem > kRoomySmem ? smem : kRoomySmem);
   if (e0 != cudaSuccess) return e0;
-  digest_parts_kernel<K, NST, SS, GP, TRIPS><<<grid, GP == 1 ? 96 : 256, pad > (size_t)smem ? pad : (size_t)smem, st>>>(m, a);
+  digest_parts_kernel<K, NST, SS, BPS, GP, TRIPS><<<grid, GP == 1 ? 96 : 256, pad > (size_t)smem ? pad : (size_t)smem, st>>>(m, a);
   return cudaGetLastError();
 }
 
@@ -689,11 +689,11 @@ static int launch_uniform(int ai, const void* d_base, uint64_t stride, uint64_t 
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     cudaError_t e;
     if (groups <= (uint32_t)sms) {  // one group per CTA; `grid` is already padded to one CTA per SM and salted
-      e = g_opts.parts_trips == 4 ? launch_parts<2, 2, 4, 1, 4>(tmap, a, grid, pad, st) : launch_parts<2, 2, 4, 1, 2>(tmap, a, grid, pad, st);
-    } else {                        // two groups per CTA, one CTA per SM (its shared memory does not leave room for two)
+      e = g_opts.parts_trips == 4 ? launch_parts<2, 2, 2, 2, 1, 4>(tmap, a, grid, pad, st) : launch_parts<2, 2, 2, 2, 1, 2>(tmap, a, grid, pad, st);
+    } else {                        // two groups per CTA, at most one CTA per group pair and SM
       a.salt = 0;
-      e = g_opts.parts_trips == 4 ? launch_parts<2, 2, 3, 2, 4>(tmap, a, (groups + 1u) / 2u, 0, st)
-                                  : launch_parts<2, 2, 3, 2, 2>(tmap, a, (groups + 1u) / 2u, 0, st);
+      e = g_opts.parts_trips == 4 ? launch_parts<2, 2, 2, 2, 2, 4>(tmap, a, (groups + 1u) / 2u, 0, st)
+                                  : launch_parts<2, 2, 2, 2, 2, 2>(tmap, a, (groups + 1u) / 2u, 0, st);
     }
     return e == cudaSuccess ? TH_OK : TH_ECUDA;
   }
@@ -704,7 +704,9 @@ static int launch_uniform(int ai, const void* d_base, uint64_t stride, uint64_t 
       case 2: e = ai == 0 ? launch_assist<Sha1, 4, 4, 4>(tmap, a, grid, 64, pad, st) : launch_assist<Sha256, 4, 4, 4>(tmap, a, grid, 64, pad, st); break;
       case 3: e = ai == 0 ? launch_assist<Sha1, 4, 4, 7>(tmap, a, grid, 64, pad, st) : launch_assist<Sha256, 4, 4, 7>(tmap, a, grid, 64, pad, st); break;
       case 4: e = ai == 0 ? launch_assist<Sha1, 2, 4, 2>(tmap, a, grid, 64, pad, st) : launch_assist<Sha256, 2, 4, 2>(tmap, a, grid, 64, pad, st); break;
-      default: e = ai == 0 ? launch_assist<Sha1, 2, 2, 4>(tmap, a, grid, 64, pad, st) : launch_assist<Sha256, 2, 2, 4>(tmap, a, grid, 64, pad, st); break;
+      case 5: e = ai == 0 ? launch_assist<Sha1, 2, 2, 3, 2>(tmap, a, grid, 64, pad, st) : launch_assist<Sha256, 2, 2, 3, 2>(tmap, a, grid, 64, pad, st); break;  // 3 slots of 2 blocks
+      case 7: e = ai == 0 ? launch_assist<Sha1, 2, 2, 4>(tmap, a, grid, 64, pad, st) : launch_assist<Sha256, 2, 2, 4>(tmap, a, grid, 64, pad, st); break;  // round 1's: 4 slots of 1 block
+      default: e = ai == 0 ? launch_assist<Sha1, 2, 2, 2, 2>(tmap, a, grid, 64, pad, st) : launch_assist<Sha256, 2, 2, 2, 2>(tmap, a, grid, 64, pad, st); break;  // 2 slots of 2 blocks
     }
     return e == cudaSuccess ? TH_OK : TH_ECUDA;
   }
@@ -925,7 +927,7 @@ int th_set_option(const char* name, long long value) {
   if (!name) return TH_EINVAL;
   const std::string k(name);
   if (k == "path") { if (value < 0 || value > 4) return TH_EINVAL; th::g_opts.path = (int)value; return TH_OK; }
-  if (k == "assist_variant") { if (value < 0 || value > 4) return TH_EINVAL; th::g_opts.assist_variant = (int)value; return TH_OK; }
+  if (k == "assist_variant") { if (value < 0 || value > 7 || value == 6) return TH_EINVAL; th::g_opts.assist_variant = (int)value; return TH_OK; }
   if (k == "assist_max_groups") { if (value < 0) return TH_EINVAL; th::g_opts.assist_max_groups = (int)value; return TH_OK; }
   if (k == "workers") { if (value < 4 || value > 16 || value % 4) return TH_EINVAL; th::g_opts.workers = (int)value; return TH_OK; }
   if (k == "slice_min_groups") { if (value < 0) return TH_EINVAL; th::g_opts.slice_min_groups = (int)value; return TH_OK; }
@@ -970,7 +972,7 @@ int th_plan(uint32_t alg, uint64_t len, uint64_t stride, uint32_t n, char* out, 
   } else if (pl.path == 4) {
     snprintf(out, cap,
              "assist: %u CTAs x (chain warp + schedule-helper warp), TMA 2-D {128B x 32 msgs} x %d tiles x %d stages, "
-             "4-slot schedule ring, smem %zu B", pl.grid, pl.k, pl.nst, pl.smem);
+             "schedule ring of 2 slots x 2 blocks, smem %zu B", pl.grid, pl.k, pl.nst, pl.smem);
   } else if (pl.path == 2) {
     snprintf(out, cap, "tile%s: one-warp CTAs, TMA 2-D {128B x 32 msgs} x %d tiles x %d stages, grid %u, smem %zu B",
              pl.lone_md5 ? " (lone chains: loads of the next block run ahead of each compression)" : "", pl.k, pl.nst, pl.grid, pl.smem);

@@ -197,12 +197,12 @@ int th_sha256_batch(const void* d_base, const uint64_t* d_offsets, const uint64_
                     uint8_t* d_out32, void* stream);
 /* MD5 and SHA-256 of the same equal-length, fixed-stride messages — what an S3 part needs (Content-MD5 / ETag and
  * x-amz-content-sha256; [dep] minio getHashSummer, call site lib/upload.js:45).  Where the batch is a few large
- * messages (the plan th_plan reports as "assist": at most 296 groups of 32) ONE kernel produces both: the chain
- * warp runs SHA-256's rounds, and the helper warp that expands its message schedule also runs the MD5 chain on the
- * words it already holds, so the parts are read from HBM once and MD5 takes no sub-partition of its own.
- * th_md5_sha256_fused says whether a batch gets that kernel (1) or the two separate launches, one after the other on
- * `stream` (0) — callers that want the separate kernels to overlap launch th_md5_batch / th_sha256_batch on two
- * streams themselves, as th_submit does. */
+ * messages (the SHA-256 plan th_plan reports as "assist": at most 296 groups of 32) ONE kernel produces both: per
+ * group a SHA-256 chain warp, the helper warp that expands its message schedule, and an MD5 chain warp, each on a
+ * sub-partition of its own; the MD5 warp and the helper read the same shared-memory tiles, so the parts are read from
+ * HBM once.  th_md5_sha256_fused says whether a batch gets that kernel (1) or the two separate launches, one after the
+ * other on `stream` (0) — callers that want the separate kernels to overlap launch th_md5_batch / th_sha256_batch on
+ * two streams themselves, as th_submit does. */
 int th_md5_sha256_batch(const void* d_base, uint64_t stride, uint64_t len, uint32_t n, uint8_t* d_out16,
                         uint8_t* d_out32, void* stream);
 int th_md5_sha256_fused(uint64_t stride, uint64_t len, uint32_t n);
@@ -259,7 +259,9 @@ int th_set_tiling(uint32_t alg, int tiles_per_stage, int stages);
  * path 3; "sliced_min_groups" / "assist_max_groups" / "tile_many_groups" auto thresholds (in 32-message groups);
  * "ragged_rows" 1 (default) cooperative cp.async row tiles | 0 one bulk copy per lane (th_set_staging geometry)
  * for batches of unlike lengths; "rows_variant" 0..4 = (tiles, stages) (1,3) (1,4) (2,2) (2,3) (4,2) of the former;
- * "fuse_md5_sha256" 1 (default) | 0: whether MD5 | SHA-256 of few large messages share one kernel. */
+ * "fuse_md5_sha256" 1 (default) | 0: whether MD5 | SHA-256 of few large messages share one kernel; "parts_trips" 4 | 2:
+ * trips the SHA-256 rounds are rolled into in that kernel; "md5_lone" 1 | 0: run-ahead stream for MD5 chains that have a
+ * sub-partition to themselves; "assist_variant" 0 (2 ring slots of 2 blocks), 1..5, 7 other geometries. */
 int th_set_option(const char* name, long long value);
 /* Describes, as text, the kernel and geometry an equal-length batch of n messages would be run
  * with on the current device (what benchmarks record next to their numbers). */

@@ -181,13 +181,16 @@ def test_uniform_batch_paths_and_tilings(torch, L, path, k, nst):
         L.th_set_tiling(7, 1, 3)
 
 
-def test_assist_kernel_schedule_offload(torch, L):
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5, 7])
+def test_assist_kernel_schedule_offload(torch, L, variant):
     """Few large messages: chain warp + schedule-helper warp per group (path 4, SHA-1 / SHA-256; MD5 has no
-    schedule and takes the tile kernel).  Lengths cover: fewer blocks than ring slots, exact block / tile /
+    schedule and takes the tile kernel), in every compiled geometry (tiles, stages, ring slots; the default and variant
+    5 hand over two blocks per slot, 7 is round 1's four slots of one block).  Lengths cover: fewer blocks than ring slots, odd block counts, exact block / tile /
     stage multiples, both padding-block cases, a ragged last group."""
     try:
         assert L.th_set_option(b"path", 4) == 0
-        cases = [(5, 1024), (33, 1024 + 55), (40, 1024 + 56), (64, 2048), (7, 4096 + 63), (100, 65536 + 64), (3, (1 << 20) + 9)]
+        assert L.th_set_option(b"assist_variant", variant) == 0
+        cases = [(5, 1024), (33, 1024 + 55), (40, 1024 + 56), (64, 2048), (9, 2048 + 64), (7, 4096 + 63), (100, 65536 + 64), (3, (1 << 20) + 9)]
         for n, ln in cases:
             stride = (ln + 15) & ~15
             d = torch.zeros(n * stride, dtype=torch.uint8, device="cuda")
@@ -212,6 +215,7 @@ def test_assist_kernel_schedule_offload(torch, L):
             assert np.nonzero(~bits)[0].tolist() == [n - 1], (n, ln)
     finally:
         L.th_set_option(b"path", 0)
+        L.th_set_option(b"assist_variant", 0)
 
 
 @pytest.mark.parametrize("n,ln", [(1, 1024), (5, 4096 + 55), (33, 100000 + 56), (64, (1 << 20) + 63), (40, 262144), (3, 1 << 20), (7, 16 << 20)])
