@@ -724,7 +724,8 @@ def extra_workloads(E, args):
                            "fill point: %d x 16 MiB parts (%.0f GiB) per GPU = %d groups, a chain warp + a helper warp on every pair of SM "
                            "sub-partitions; north_star's >= 70 %% bar is stated on 16 MiB-part batches; messages [0, 4096) are configs[2]'s"
                            % (nf, nf * ln / 2**30, (nf + 31) // 32),
-                           first, steps, warmup, False, "sample", data=data, variants=["sha1", "md5", "sha256"], known=digs)
+                           first, steps, warmup, False, "sample", data=data, variants=["sha1", "md5", "sha256"], known=digs,
+                           counters_key="parts_fill_point" if nf == FILL_POINT_PARTS else None)
     fill["scaling"] = "weak"
     out.append(fill)
     del data

@@ -355,6 +355,35 @@ def test_one_pass_feeds_pieces_and_parts_from_the_same_slot(eng, tmp_path):
     assert s1["submits"] - s0["submits"] == 2 * 3 and s1["bytes"] - s0["bytes"] == 2 * size
 
 
+def test_o_direct_reads_and_files_dealt_to_gpus(eng, tmp_path):
+    """reader.hash_file_parts(direct=True): the 4 KiB-aligned bodies of the chunks come through O_DIRECT straight into
+    the pinned slots (where the file system takes it), the digests are the file's; reader.hash_media_files deals whole
+    files to the context's GPUs (here: the one there is) with a feeder thread and reader pool per GPU."""
+    from downloader_b200 import ALG_MD5, ALG_SHA1, ALG_SHA256, reader, s3
+    sizes = [9 * MiB + 4321, 5 * MiB, 3 * MiB + 1]
+    paths, datas = [], []
+    for i, n in enumerate(sizes):
+        p = str(tmp_path / f"m{i}.bin")
+        datas.append(make_file(p, 300 + i, n).tobytes())
+        paths.append(p)
+    ranges = s3.part_ranges(sizes[0], 4 * MiB)
+    for direct in (False, True):
+        r = reader.hash_file_parts(eng, paths[0], ranges, ALG_MD5 | ALG_SHA256, batch_bytes=8 * MiB, direct=direct)
+        for k, (a, b) in enumerate(ranges):
+            assert bytes(r[ALG_MD5][k]) == hashlib.md5(datas[0][a:b]).digest(), (direct, k)
+            assert bytes(r[ALG_SHA256][k]) == hashlib.sha256(datas[0][a:b]).digest(), (direct, k)
+    jobs = [dict(path=p, piece_length=MiB, expected_sha1=None, part_ranges=s3.part_ranges(n, 4 * MiB), batch_bytes=8 * MiB, direct=True)
+            for p, n in zip(paths, sizes)]
+    out = reader.hash_media_files(eng, jobs, gpus=[0])
+    assert [o["gpu"] for o in out] == [0, 0, 0]
+    for o, d, n in zip(out, datas, sizes):
+        for k in range(-(-n // MiB)):
+            assert bytes(o["pieces"][ALG_SHA1][k]) == hashlib.sha1(d[k * MiB:(k + 1) * MiB]).digest()
+        for k, (a, b) in enumerate(s3.part_ranges(n, 4 * MiB)):
+            assert bytes(o["parts"][ALG_MD5][k]) == hashlib.md5(d[a:b]).digest()
+        assert o["read"]["direct_bytes"] + o["read"]["buffered_bytes"] == n
+
+
 def test_one_context_drives_two_gpus(tmp_path):
     """th_init with a GPU list: per-GPU rings/streams in one process, pieces sharded by index."""
     import torch
