@@ -522,7 +522,7 @@ struct TileOpts {
   int tile_many_groups = 8192;  // auto: SHA-1 / SHA-256 batches with at least this many groups go back to one-warp CTAs
                                 // (many waves balance themselves and measured 1-12 % faster than the persistent kernel)
   int md5_lone = 1;             // MD5 with at most one group per SM sub-partition: the run-ahead stream (tile_stream_lone)
-  int parts_trips = 4;          // digest_parts_kernel: SHA-256 rounds as 4 trips of 16 (4.5 KB of code; measured 243 ms per 16 MiB part) or 2 of 32 (8.7 KB; 262 ms)
+  int parts_variant = 0;        // digest_parts_kernel tile geometry: 0 = 2 tiles x 2 stages, 1 = 4 x 2, 2 = 2 x 3 (tuning)
   int fuse_md5_sha256 = 1;      // th_md5_sha256_batch: 1 = one launch (digest_parts_kernel) where the SHA-256 plan is "assist"
   int ragged_rows = 1;          // per-lane kernels: 1 = cooperative cp.async row tiles, 0 = one bulk copy per lane
   int rows_variant[3] = {2, 2, 2};  // index into g_rows_variants per digest
@@ -689,11 +689,14 @@ static int launch_uniform(int ai, const void* d_base, uint64_t stride, uint64_t 
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     cudaError_t e;
     if (groups <= (uint32_t)sms) {  // one group per CTA; `grid` is already padded to one CTA per SM and salted
-      e = g_opts.parts_trips == 4 ? launch_parts<2, 2, 2, 2, 1, 4>(tmap, a, grid, pad, st) : launch_parts<2, 2, 2, 2, 1, 2>(tmap, a, grid, pad, st);
+      e = g_opts.parts_variant == 1   ? launch_parts<4, 2, 2, 2, 1, 4>(tmap, a, grid, pad, st)
+          : g_opts.parts_variant == 2 ? launch_parts<2, 3, 2, 2, 1, 4>(tmap, a, grid, pad, st)
+                                      : launch_parts<2, 2, 2, 2, 1, 4>(tmap, a, grid, pad, st);
     } else {                        // two groups per CTA, at most one CTA per group pair and SM
       a.salt = 0;
-      e = g_opts.parts_trips == 4 ? launch_parts<2, 2, 2, 2, 2, 4>(tmap, a, (groups + 1u) / 2u, 0, st)
-                                  : launch_parts<2, 2, 2, 2, 2, 2>(tmap, a, (groups + 1u) / 2u, 0, st);
+      e = g_opts.parts_variant == 1   ? launch_parts<4, 2, 2, 2, 2, 4>(tmap, a, (groups + 1u) / 2u, 0, st)
+          : g_opts.parts_variant == 2 ? launch_parts<2, 3, 2, 2, 2, 4>(tmap, a, (groups + 1u) / 2u, 0, st)
+                                      : launch_parts<2, 2, 2, 2, 2, 4>(tmap, a, (groups + 1u) / 2u, 0, st);
     }
     return e == cudaSuccess ? TH_OK : TH_ECUDA;
   }
@@ -936,7 +939,7 @@ int th_set_option(const char* name, long long value) {
   if (k == "sliced_min_groups") { if (value < 1) return TH_EINVAL; th::g_opts.sliced_min_groups = (int)value; return TH_OK; }
   if (k == "ragged_rows") { if (value < 0 || value > 1) return TH_EINVAL; th::g_opts.ragged_rows = (int)value; return TH_OK; }
   if (k == "md5_lone") { if (value < 0 || value > 1) return TH_EINVAL; th::g_opts.md5_lone = (int)value; return TH_OK; }
-  if (k == "parts_trips") { if (value != 2 && value != 4) return TH_EINVAL; th::g_opts.parts_trips = (int)value; return TH_OK; }
+  if (k == "parts_variant") { if (value < 0 || value > 2) return TH_EINVAL; th::g_opts.parts_variant = (int)value; return TH_OK; }
   if (k == "fuse_md5_sha256") { if (value < 0 || value > 1) return TH_EINVAL; th::g_opts.fuse_md5_sha256 = (int)value; return TH_OK; }
   if (k == "rows_variant") {
     if (value < 0 || value >= th::kNumRowsVariants) return TH_EINVAL;

@@ -259,8 +259,8 @@ int th_set_tiling(uint32_t alg, int tiles_per_stage, int stages);
  * path 3; "sliced_min_groups" / "assist_max_groups" / "tile_many_groups" auto thresholds (in 32-message groups);
  * "ragged_rows" 1 (default) cooperative cp.async row tiles | 0 one bulk copy per lane (th_set_staging geometry)
  * for batches of unlike lengths; "rows_variant" 0..4 = (tiles, stages) (1,3) (1,4) (2,2) (2,3) (4,2) of the former;
- * "fuse_md5_sha256" 1 (default) | 0: whether MD5 | SHA-256 of few large messages share one kernel; "parts_trips" 4 | 2:
- * trips the SHA-256 rounds are rolled into in that kernel; "md5_lone" 1 | 0: run-ahead stream for MD5 chains that have a
+ * "fuse_md5_sha256" 1 (default) | 0: whether MD5 | SHA-256 of few large messages share one kernel; "parts_variant" 0..2:
+ * tile geometry of that kernel (2 tiles x 2 stages | 4 x 2 | 2 x 3); "md5_lone" 1 | 0: run-ahead stream for MD5 chains that have a
  * sub-partition to themselves; "assist_variant" 0 (2 ring slots of 2 blocks), 1..5, 7 other geometries. */
 int th_set_option(const char* name, long long value);
 /* Describes, as text, the kernel and geometry an equal-length batch of n messages would be run

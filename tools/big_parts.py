@@ -29,7 +29,7 @@ def main():
     ap.add_argument("--only", default="", help="one of sha1, md5, sha256, md5+sha256")
     ap.add_argument("--iters", type=int, default=2)
     ap.add_argument("--no-verify", action="store_true")
-    ap.add_argument("--opt", action="append", default=[], help="th_set_option name=value (tuning), e.g. parts_trips=4")
+    ap.add_argument("--opt", action="append", default=[], help="th_set_option name=value (tuning), e.g. parts_variant=1")
     ap.add_argument("--no-fuse", action="store_true", help="MD5 + SHA-256 as two kernels on two streams instead of the one-launch kernel")
     a = ap.parse_args()
     L = _capi.lib()
