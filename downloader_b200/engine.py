@@ -38,6 +38,7 @@ class Engine:
         self.ring_bytes = ring_bytes
         self.device_bytes = device_bytes or ring_bytes
         self._cbs = {}
+        self._retired_cbs = []  # thunks of retired tickets: result() may run INSIDE the callback, whose thunk must outlive it
 
     # -- lifecycle ------------------------------------------------------------------------------
     def close(self) -> None:
@@ -148,7 +149,11 @@ class Engine:
 
         rc = self._L.th_result(self._ctx, ticket, p(ALG_SHA1), p(ALG_MD5), p(ALG_SHA256),
                                ok.ctypes.data if ok is not None else None)
-        self._cbs.pop(ticket, None)
+        cb = self._cbs.pop(ticket, None)
+        if cb is not None:  # freed a little later, never while it may still be executing
+            self._retired_cbs.append(cb)
+            if len(self._retired_cbs) > 256:
+                del self._retired_cbs[:128]
         check(rc, "th_result", self._ctx)
         out.update(bufs)
         if ok is not None:

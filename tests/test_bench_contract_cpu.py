@@ -36,3 +36,17 @@ def test_reference_arm_under_torchrun_prints_once():
     assert r.returncode == 0, r.stderr[-2000:]
     lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
     assert len(lines) == 1 and json.loads(lines[0])["n_gpus"] == 2
+
+
+def test_device_order_takes_gpus_from_both_halves_of_the_box():
+    """bench.py --device-order auto: rank r's GPU alternates between the two halves of the device list (the two host
+    bridges of this pool's 8-GPU boxes, profiles/r2_h2d_probe_8gpu.jsonl); every rank still gets its own device."""
+    sys.path.insert(0, ROOT)
+    import bench
+    order, why = bench.device_order("auto", 8, 4)
+    assert order[:4] == [0, 4, 1, 5] and "halves" in why
+    assert sorted(bench.device_order("auto", 8, 8)[0]) == list(range(8))
+    assert bench.device_order("auto", 8, 2)[0][:2] == [0, 4]
+    assert bench.device_order("auto", 1, 1)[0] == [0] and bench.device_order("auto", 2, 2)[0] == [0, 1]
+    assert bench.device_order("identity", 8, 4)[0][:4] == [0, 1, 2, 3]
+    assert bench.device_order("3,2,1,0", 8, 4) == ([3, 2, 1, 0], "given on the command line")
