@@ -827,6 +827,8 @@ struct Assist<Sha1> {
   }
   // V = 0: x = IADD3(e, wk, f) — 4 ALU instructions per round; V = 1: x = (e + wk) + f as two IMADs — 3 ALU + 2 FMA
   // (e + wk is off the chain; the second IMAD is on it).  See Assist<Sha256>::rounds for why the mix matters.
+  // Measured per block: 702 / 780.  (rotl(b, 30) as IMAD.HI + IMAD — hi and lo word of b * 2^30 — to take the fourth
+  // instruction off the ALU pipe: 965; IMAD.HI is no full-rate instruction.)
   template <int V = 0, int KH_ = KH>
   __device__ static __forceinline__ void rounds(uint32_t* h, const uint4* src, uint32_t one) {
     uint32_t a = h[0], b = h[1], c = h[2], d = h[3], e = h[4];
