@@ -269,3 +269,123 @@ def test_o_direct_reads_give_the_same_bytes_as_buffered_reads(tmp_path):
                 assert src.direct_bytes > 0  # this file system takes O_DIRECT: the aligned bodies used it
         finally:
             src.close()
+
+
+# ---- job runner: the Python mirror of lib/main.js's stage loop runs; js/lib/main.js is checked to have the same shape ----
+class _Msg:
+    def __init__(self, content=b"job"):
+        self.content, self.acked, self.nacked = content, 0, 0
+
+    def ack(self):
+        self.acked += 1
+
+    def nack(self):
+        self.nacked += 1
+
+
+class _Codec:
+    def decode_download(self, content):
+        return {"media": {"id": "job-1", "type": 0}}
+
+    def encode_convert(self, payload):
+        return repr(sorted(payload)).encode()
+
+
+class _Queue:
+    def __init__(self, fail=False):
+        self.sent, self.fail = [], fail
+
+    def publish(self, topic, body):
+        if self.fail:
+            raise ConnectionError("broker gone")
+        self.sent.append((topic, body))
+
+
+class _S3:
+    def __init__(self, done=False):
+        self.done, self.asked = done, []
+
+    def getObject(self, bucket, key):
+        self.asked.append((bucket, key))
+        if not self.done:
+            raise KeyError("NoSuchKey")
+        return b"true"
+
+
+def _runner(s3, queue, behaviour):
+    from downloader_b200.stages import _NullTelem
+    from downloader_b200.stages import main as main_stage
+    calls = []
+
+    def make(name):
+        async def fac(config, emitter, logger):
+            async def stage(job):
+                calls.append((name, dict(job.get("lastStage") or {})))
+                if behaviour.get(name) is not None:
+                    raise behaviour[name]
+                return {"from": name}
+            return stage
+        return fac
+    tel = _NullTelem()
+    cfg = {"telem": tel, "s3": s3, "queue": queue, "codec": _Codec()}
+    handle = run(main_stage.factory(cfg, MockLogger(), factories={n: make(n) for n in main_stage.STAGES}))
+    return handle, calls, tel
+
+
+def test_job_runner_runs_stages_in_order_and_publishes():
+    s3, q = _S3(done=False), _Queue()
+    handle, calls, tel = _runner(s3, q, {})
+    m = _Msg()
+    run(handle(m))
+    assert [c[0] for c in calls] == ["download", "process", "upload"]
+    assert calls[0][1] == {} and calls[1][1] == {"from": "download"} and calls[2][1] == {"from": "process"}  # lastStage threading
+    assert s3.asked == [("triton-staging", "job-1/original/done")]
+    assert [t for t, _ in q.sent] == ["v1.convert"] and (m.acked, m.nacked) == (1, 0)
+    assert tel.events[0] == ("job-1", "status", 2)
+
+
+def test_job_runner_skips_a_job_that_is_already_staged():
+    """lib/main.js:117-124,153-155: the `done` marker exists -> no stage runs, the convert job is published again, ack."""
+    s3, q = _S3(done=True), _Queue()
+    handle, calls, _ = _runner(s3, q, {})
+    m = _Msg()
+    run(handle(m))
+    assert calls == [] and len(q.sent) == 1 and (m.acked, m.nacked) == (1, 0)
+
+
+def test_job_runner_error_policy_matches_the_reference():
+    """lib/main.js:141-151,157-166: a stalled download is acked and dropped; any other stage error -> status 6 + nack,
+    nothing published; a failed publish is only logged — neither ack nor nack, no ERRORED status."""
+    from downloader_b200.stages.download import DownloadStalled
+    handle, calls, tel = _runner(_S3(), _Queue(), {"download": DownloadStalled("Download stalled.")})
+    m = _Msg()
+    run(handle(m))
+    assert (m.acked, m.nacked) == (1, 0) and [c[0] for c in calls] == ["download"] and ("job-1", "status", 6) not in tel.events
+    q = _Queue()
+    handle, calls, tel = _runner(_S3(), q, {"process": RuntimeError("Failed to find any suitable media files")})
+    m = _Msg()
+    run(handle(m))
+    assert (m.acked, m.nacked) == (0, 1) and q.sent == [] and tel.events[-1] == ("job-1", "status", 6)
+    handle, calls, tel = _runner(_S3(), _Queue(fail=True), {})
+    m = _Msg()
+    run(handle(m))
+    assert (m.acked, m.nacked) == (0, 0) and len(calls) == 3 and ("job-1", "status", 6) not in tel.events
+
+
+def test_js_main_has_the_shape_of_the_mirror_that_runs():
+    """js/lib/main.js cannot be executed here; check the order of its steps against the Python mirror's: done-marker
+    lookup before the stage loop, ERRDLSTALL -> ack and otherwise ERRORED + nack inside the stage try/catch, and the
+    publish in a try/catch of its own that neither acks nor nacks."""
+    import re
+    with open(os.path.join(ROOT, "js", "lib", "main.js")) as f:
+        js = f.read()
+    code = re.sub(r"/\*.*?\*/", "", js, flags=re.S)
+    code = "\n".join(line.split("//")[0] for line in code.splitlines())
+    assert "['download', 'process', 'upload']" in code
+    order = [code.index(k) for k in ("getObject('triton-staging', path.join(jobId, 'original/', 'done'))",
+                                     "for (const name of STAGES) lastStage = await table[name]",
+                                     "err.code === 'ERRDLSTALL'", "emitStatus(jobId, STATUS_ERRORED)",
+                                     "config.queue.publish('v1.convert'", "failed to create job:")]
+    assert order == sorted(order)
+    publish_catch = code[code.index("config.queue.publish('v1.convert'"):code.index("message.ack()\n    active--")]
+    assert "nack" not in publish_catch and "STATUS_ERRORED" not in publish_catch
