@@ -389,3 +389,31 @@ def test_js_main_has_the_shape_of_the_mirror_that_runs():
     assert order == sorted(order)
     publish_catch = code[code.index("config.queue.publish('v1.convert'"):code.index("message.ack()\n    active--")]
     assert "nack" not in publish_catch and "STATUS_ERRORED" not in publish_catch
+
+
+CONTRACT = {  # strings of the stage contract: (reference file, JS module, Python mirror)
+    "Download stalled.": ("download.js", "download.js", "download.py"),
+    "ERRDLSTALL": ("download.js", "download.js", "download.py"),
+    "File URLs are not allowed.": ("download.js", "download.js", "download.py"),
+    "Protocol not supported.": ("download.js", "download.js", "download.py"),
+    "Invalid files data type, expected array, got '": ("upload.js", "upload.js", "upload.py"),
+    "triton-staging": ("upload.js", "upload.js", "upload.py"),
+    "'original/'": ("upload.js", "upload.js", None),
+    " not found.": ("upload.js", "upload.js", "upload.py"),
+}
+
+
+def test_stage_contract_strings_are_the_same_in_reference_js_and_python():
+    """Error texts, the error code, the bucket and the object-name pieces are contract: lib/main.js and operators
+    match on them.  Each must appear in the JS module, in the Python mirror that runs, and (when the reference tree
+    is present) in the reference file it was taken from."""
+    for text, (ref, js, py) in CONTRACT.items():
+        with open(os.path.join(ROOT, "js", "lib", js)) as f:
+            assert text in f.read(), (text, js)
+        if py:
+            with open(os.path.join(ROOT, "downloader_b200", "stages", py)) as f:
+                assert text.strip("'") in f.read(), (text, py)
+        refp = os.path.join("/root/reference/lib", ref)
+        if os.path.exists(refp):
+            with open(refp) as f:
+                assert text in f.read(), (text, ref)
